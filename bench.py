@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the force path (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Headline workload (configs[1]): direct all-pairs, N = 1,048,576, Leapfrog (Verlet_DKD), FP32, bodies
+target-sharded over the GPUs with one NCCL all-gather of positions per force evaluation.  One "step" is
+one Leapfrog step = half drift, all-gather, one force evaluation (N^2 interactions in total), kick + half
+drift.  `value` = interactions per second of the whole job, inputs resident in HBM.  The same line carries
+the Barnes-Hut metric (steps/s, N = 1,048,576, theta = 0.5, configs[2]) under "bh".
+
+--impl reference: the reference has no CPU implementation (it is GPU-only), so this
+arm times the OpenMP port of its loops (oracle/nbody_oracle.c) on the host cores, on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as graft  # noqa: E402
+
+N_BODIES = 1 << 20
+EPS = 1.01
+DT = 0.001
+THETA = 0.5
+FLOP_PER_INTERACTION = {3: 20.0, 2: 14.0}   # SURVEY.md section 8d / BASELINE.md section 4
+SM_COUNT, FP32_LANES, MAX_MHZ = 148, 128, 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])), mx.append(float(r[2])), pw.append(float(r[3]))
+                for k, nm in enumerate(names):
+                    if r[5 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_reference_arm(args):
+    """Host-core arm: OpenMP port of the reference loops (kind 'port': the reference itself is GPU-only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg = graft.load_package()
+    oracle = graft.load_oracle()
+    cores = oracle.max_threads()
+    pos = pkg.ics.uniform_disk(N_BODIES, seed=1, z_half_height=3000.0)
+    sample_targets = 2048
+    times = []
+    for it in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        oracle.direct_f32(pos, 3, EPS, t0=(it * sample_targets) % (N_BODIES - sample_targets), nt=sample_targets,
+                          fast=True)
+        dt = time.perf_counter() - t0
+        if it >= args.warmup:
+            times.append(dt)
+    inter = float(sample_targets) * N_BODIES
+    val = inter * len(times) / sum(times)
+    sample = f"{sample_targets} targets x {N_BODIES} sources per step (1/512 of one force evaluation), OpenMP, FP32"
+    line = {"impl": "reference", "metric": "interactions/s (direct, N=1M)", "value": val, "unit": "interactions/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "direct all-pairs N=1048576 uniform disk (R3), Leapfrog force evaluation", "n": N_BODIES,
+                       "softening": EPS},
+            "cpu_baseline": {"value": val, "unit": "interactions/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference is GPU-only; this arm is the OpenMP transcription of its direct loop (oracle/)"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=N_BODIES, help="bodies (parity / tuning runs only; default = headline)")
+    ap.add_argument("--dim", type=int, default=3)
+    ap.add_argument("--skip-bh", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-refcuda", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = graft.load_package()
+    n, dim = args.n, args.dim
+    eng = pkg.Engine(local, n)
+    dev = torch.device("cuda", local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- state: replicated positions, slice-local velocities / accelerations --------------------------
+    pos_h = pkg.ics.uniform_disk(n, seed=1, z_half_height=3000.0 if dim == 3 else 0.0)
+    begin = (n * rank) // world
+    end = (n * (rank + 1)) // world
+    count = end - begin
+    pos = torch.from_numpy(pos_h).to(dev)
+    acc = torch.zeros(count, 4, device=dev)
+    vel = torch.zeros(count, 4, device=dev)
+    equal = (n % world == 0)
+    sizes = [(n * (r + 1)) // world - (n * r) // world for r in range(world)]
+
+    def gather_positions():
+        if world == 1:
+            return
+        if equal:
+            dist.all_gather_into_tensor(pos, pos[begin:end])       # in place, NCCL over NVLink
+        else:
+            outs = list(torch.split(pos, sizes, dim=0))
+            dist.all_gather(outs, pos[begin:end].clone())
+
+    def force():
+        eng.direct_accel_slice(pos, begin, count, acc, dim, EPS)
+
+    # initial velocities: tangential, from one force evaluation (DiskModel, src/InitialConditions.cu:160-192)
+    force()
+    torch.cuda.synchronize()
+    vel.copy_(torch.from_numpy(pkg.ics.disk_velocities(pos_h[begin:end], acc.cpu().numpy(), space_r3=(dim == 3))))
+    launches_force = eng.direct_last_launch()["launches"]
+
+    def step():
+        eng.verlet_dkd_drift(pos, vel, begin, count, DT)
+        gather_positions()
+        force()
+        eng.verlet_dkd_kick_drift(pos, vel, acc, begin, count, DT)
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b in ev:
+            flush.fill_(1)          # L2 flush between timed iterations (outside the event pair)
+            a.record()
+            fn()
+            b.record()
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    total_ms = timed(step, args.steps, args.warmup)
+    # kernel-only time of the dominant kernel (the force evaluation of this rank's slice), same stream
+    kern_ms = timed(force, args.steps, 1) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    interactions = float(n) * float(n)
+    value = interactions * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through the host-buffer C-ABI call ---------------------------------------------------
+    pos_pin = torch.from_numpy(pos_h).pin_memory()
+    acc_pin = torch.empty(n, 4).pin_memory()
+
+    def e2e_step():
+        # every rank uploads all positions, evaluates, downloads; the C ABI call synchronises
+        eng.direct_accel_host(pos_pin, dim, EPS, out=acc_pin)
+
+    if world == 1:
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        e2e = {"value": interactions * args.steps / (e2e_ms * 1e-3), "unit": "interactions/s",
+               "h2d_bytes_per_step": n * 16, "d2h_bytes_per_step": n * 16,
+               "call": "nb_direct_accel_host (pinned host float4[n] in, float4[n] out)"}
+    else:
+        # sharded end-to-end: upload the full positions, evaluate the rank's slice, download the slice
+        acc_slice_pin = torch.empty(count, 4).pin_memory()
+
+        def e2e_sharded():
+            pos.copy_(pos_pin, non_blocking=True)
+            force()
+            acc_slice_pin.copy_(acc, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        for _ in range(2):
+            e2e_sharded()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_sharded()
+        barrier()
+        t = torch.tensor([(time.perf_counter() - t0) * 1e3], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": interactions * args.steps / (float(t.item()) * 1e-3), "unit": "interactions/s",
+               "h2d_bytes_per_step": n * 16, "d2h_bytes_per_step": count * 16,
+               "call": "pinned H2D of all positions + nb_direct_accel_slice + pinned D2H of the slice, per rank"}
+
+    # ---- roofline of the dominant kernel -----------------------------------------------------------------
+    flop = FLOP_PER_INTERACTION[dim]
+    slice_inter = float(count) * float(n)
+    achieved = slice_inter * flop / (kern_ms * 1e-3) / 1e12
+    peak = SM_COUNT * FP32_LANES * 2 * MAX_MHZ * 1e6 / 1e12
+    roofline = {"bound": "fp32", "kernel": f"direct_kernel<{dim}D> (+pack, +partial reduce)", "achieved": achieved,
+                "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": "148 SMs x 128 FP32 lanes x 2 x 1965 MHz (clocks.max.sm); MEASURED_PEAKS.json has no FP32 entry",
+                "kernel_ms": kern_ms, "flop_per_interaction": flop,
+                "fp32_pipe_ops_per_interaction": 12 if dim == 3 else 8,
+                "launch": eng.direct_last_launch()}
+    if rank == 0 and clocks and clocks.get("sm_mhz"):
+        roofline["frac_at_observed_clock"] = achieved / (SM_COUNT * FP32_LANES * 2 * clocks["sm_mhz"] * 1e6 / 1e12)
+
+    extra = {}
+    if rank == 0:
+        try:
+            cal = eng.calibrate()
+            roofline["calibrated"] = cal
+            roofline["frac_of_calibrated_ffma"] = achieved / max(cal["ffma_tflops"], cal["ffma2_tflops"])
+        except Exception as e:  # calibration is informative only
+            roofline["calibrated"] = str(e)
+
+    # ---- the reference's own CUDA kernel on the same box (informative; north_star parity target) ---------
+    if rank == 0 and world == 1 and not args.skip_refcuda:
+        so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
+        if os.path.exists(so) and n % 128 == 0:
+            import ctypes as C
+            ref = C.CDLL(so)
+            ref.ref_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float]
+            acc_ref = torch.zeros(n, 4, device=dev)
+            ref.ref_direct(pos.data_ptr(), acc_ref.data_ptr(), n, dim, EPS)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ref.ref_direct(pos.data_ptr(), acc_ref.data_ptr(), n, dim, EPS)   # legacy default stream
+            torch.cuda.synchronize()
+            ref_ms = (time.perf_counter() - t0) * 1e3
+            extra["reference_cuda_kernel"] = {"interactions_per_s": interactions / (ref_ms * 1e-3), "ms": ref_ms,
+                                              "what": "unmodified src/DirectComputeKernels.cu built for sm_100, same box"}
+
+    # ---- Barnes-Hut metric ---------------------------------------------------------------------------------
+    if not args.skip_bh:
+        try:
+            p2 = torch.from_numpy(pkg.ics.uniform_disk(N_BODIES, seed=1)).to(dev)
+            a2 = torch.zeros(N_BODIES, 4, device=dev)
+            groups = (N_BODIES + 31) // 32
+            g0, g1 = (groups * rank) // world, (groups * (rank + 1)) // world
+
+            def bh_step():
+                eng.bh_accel_groups(p2, a2, THETA, EPS, g0, g1 - g0)
+            bh_ms = timed(bh_step, max(args.steps, 10), 3) / max(args.steps, 10)
+            extra["bh"] = {"metric": "BH steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
+                           "ms_per_step": bh_ms, "counters": eng.bh_last_counters() if rank == 0 else None}
+        except pkg.NbodyError as e:
+            extra["bh"] = {"unavailable": str(e)}
+
+    # ---- host baseline (rank 0, N=1 only) ----------------------------------------------------------------
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        oracle = graft.load_oracle()
+        nt = 4096
+        oracle.direct_f32(pos_h, dim, EPS, t0=0, nt=256, fast=True)
+        t0 = time.perf_counter()
+        oracle.direct_f32(pos_h, dim, EPS, t0=0, nt=nt, fast=True)
+        dt_cpu = time.perf_counter() - t0
+        cpu_baseline = {"value": nt * float(n) / dt_cpu, "unit": "interactions/s", "cores": oracle.max_threads(),
+                        "kind": "port",
+                        "sample": f"{nt} targets x {n} sources (1/{n // nt} of one evaluation), OpenMP FP32 port of "
+                                  "src/DirectComputeKernels.cu:60-68"}
+
+    if rank == 0:
+        line = {"metric": "interactions/s (direct, N=1M)", "value": value, "unit": "interactions/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"direct all-pairs N={n} uniform disk (R{dim}), Leapfrog (Verlet_DKD) step, "
+                                       f"target-sharded over {world} GPU(s), one NCCL all-gather of positions per step",
+                           "n": n, "softening": EPS, "dt": DT, "l2": "flushed between timed iterations (256 MB write)",
+                           "parallelism": f"target-slice x{world}"},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (launches_force + 2),
+                "roofline": roofline, "cpu_baseline": cpu_baseline}
+        line.update(extra)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    eng.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,153 @@
+/*
+ * nbody_b200.h -- C ABI of the B200-native gravitational force engine.
+ *
+ * Drop-in boundary for the force path of MoonArchitect/N-body-simulation (reference paths below are
+ * relative to that repository).  The reference reaches its force kernels through three free functions
+ * taking raw device pointers:
+ *
+ *     void direct2DCompute (float4* pos, float4* acc, int n, const float SOFTENING);   src/DirectComputeKernels.cuh:7
+ *     void direct3DCompute (float4* pos, float4* acc, int n, const float SOFTENING);   src/DirectComputeKernels.cuh:12
+ *     void barnesHutCompute(float4* pos, float4* acc, float4* d_bounds, int* index, int* nodes,
+ *                           int* sortedIdx, int* SFCkeys, int n, int m, float theta,
+ *                           const float SOFTENING);                                     src/BarnesHutKernels.cuh:5
+ *
+ * called only from ComputeMethods::Direct::computeAcc / BarnesHut::computeAcc (src/ComputeMethods.cpp:21,23,48).
+ * The entry points here replace exactly those calls.  Conventions:
+ *   - plain C: opaque handle, int status (0 = NB_OK), pointers and sizes only, no C++ or torch types;
+ *   - body layout = the reference's float4 (x, y, z, mass), G = 1, softening added un-squared to r^2
+ *     (src/DirectComputeKernels.cu:26,64); `dim` 2 selects the reference's 2D law m*d/(eps+r^2), 3 the
+ *     Newtonian m*d/(eps+r^2)^(3/2);
+ *   - `pos`/`acc` device pointers are owned by the caller (NbodySystem::device, src/NbodySystem.h:17-26);
+ *     scratch memory is owned by the handle (the reference allocates its scratch in
+ *     BarnesHut::setSystem, src/ComputeMethods.cpp:40-44);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream the reference
+ *     uses); calls are asynchronous on that stream unless stated otherwise;
+ *   - acc[i] is written as (ax, ay, az, 0); in 2D az = 0 as well (the reference leaves .z/.w
+ *     untouched, src/DirectComputeKernels.cu:34-35 -- SURVEY.md section 9);
+ *   - no CPU fallback exists: without a CUDA device every compute entry point returns an error.
+ */
+#ifndef NBODY_B200_H
+#define NBODY_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB_OK 0
+#define NB_ERR_INVALID 1   /* bad argument */
+#define NB_ERR_CUDA 2      /* a CUDA runtime call failed; see nb_last_error */
+#define NB_ERR_OVERFLOW 3  /* a device-side capacity was exceeded (tree node pool, traversal stack) */
+#define NB_ERR_NO_DEVICE 4
+
+/* flags for nb_direct_accel* */
+#define NB_DIRECT_AUTO 0      /* split the source range across CTAs when that fills the GPU better */
+#define NB_DIRECT_ORDERED 1   /* one accumulator per target, sources summed in index order 0..n-1: the
+                                 summation order of src/DirectComputeKernels.cu:16-30,52-68, bit-identical
+                                 to the reference kernel's output */
+
+/* flags for nb_bh_accel* */
+#define NB_BH_FRESH_BOUNDS 0       /* bounding box recomputed from scratch every call (fix) */
+#define NB_BH_ACCUMULATE_BOUNDS 1  /* reference behaviour: d_bounds is the running union over all calls,
+                                      src/BarnesHutKernels.cu:190-193 + src/ComputeMethods.cpp:40 */
+
+typedef struct nb_context nb_context;
+
+/* ---- lifetime ------------------------------------------------------------------------------------ */
+
+/* Creates an engine bound to CUDA device `device`.  `max_bodies` sizes the scratch memory up front
+ * (it grows on demand if a later call passes more bodies).  Replaces the cudaMalloc block of
+ * BarnesHut::setSystem (src/ComputeMethods.cpp:40-44). */
+int nb_create(nb_context** out, int device, int max_bodies);
+int nb_destroy(nb_context* ctx);
+/* Human-readable description of the last failure on this handle (or of the last failed nb_create when
+ * ctx is NULL).  Replaces the printf(cudaGetErrorString()) pattern of src/BarnesHutKernels.cu:15-17. */
+const char* nb_last_error(const nb_context* ctx);
+/* Device the handle is bound to, number of SMs, and bytes of scratch currently held. */
+int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* scratch_bytes);
+
+/* ---- direct all-pairs ---------------------------------------------------------------------------- */
+
+/* Replaces direct2DCompute / direct3DCompute (src/DirectComputeKernels.cu:5-8,41-44).
+ * pos: device float4[n]; acc: device float4[n]; any n >= 0 (the reference needs n % 128 == 0). */
+int nb_direct_accel(nb_context* ctx, const float* pos, float* acc, int n, int dim, float softening,
+                    int flags, void* stream);
+
+/* Target-slice form used for multi-GPU sharding: accelerations of bodies [target_begin,
+ * target_begin + target_count) due to ALL n sources; acc is device float4[target_count] (slice-local).
+ * No counterpart in the single-GPU reference; with target_begin = 0, target_count = n it is
+ * nb_direct_accel. */
+int nb_direct_accel_slice(nb_context* ctx, const float* pos, int n, int target_begin, int target_count,
+                          float* acc, int dim, float softening, int flags, void* stream);
+
+/* Host-buffer form: copies host float4[n] positions to the device, evaluates, copies float4[n]
+ * accelerations back and synchronises.  What NbodySystem::updateDeviceData + computeAcceleration(true)
+ * + updateHostData do around the reference kernels (src/NbodySystem.cpp:70-93). */
+int nb_direct_accel_host(nb_context* ctx, const float* host_pos, float* host_acc, int n, int dim,
+                         float softening, int flags);
+
+/* Number of source-range splits (1 = ordered) and thread blocks the last direct call used. */
+int nb_direct_last_launch(const nb_context* ctx, int* jsplit, int* blocks, int* launches);
+
+/* ---- Barnes-Hut (2D quadtree, as the reference: src/ComputeMethods.cpp:35-38 forces R2) ------------ */
+
+/* Replaces barnesHutCompute (src/BarnesHutKernels.cu:11-70): bounds -> keys -> sort -> tree -> centre of
+ * mass -> walk, one stream-ordered pipeline without host synchronisation.  pos: device float4[n],
+ * acc: device float4[n].  The tree lives in the handle's scratch; pos[n..m) is never touched. */
+int nb_bh_accel(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening,
+                int flags, void* stream);
+
+/* Sharded form: builds the tree over all n bodies, walks only the 32-target groups
+ * [group_begin, group_begin + group_count) of the sorted order (group g = sorted positions
+ * [32 g, 32 g + 32)); acc is still indexed by body id (device float4[n], only the walked bodies are
+ * written).  No counterpart in the single-GPU reference. */
+int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening,
+                       int flags, int group_begin, int group_count, void* stream);
+
+int nb_bh_accel_host(nb_context* ctx, const float* host_pos, float* host_acc, int n, float theta,
+                     float softening, int flags);
+
+/* Stage entry points (tests and profiling).  Each runs the pipeline up to and including the named
+ * stage on `pos` and copies the result to HOST memory; they synchronise.
+ *   bounds     : float[4] (minX, minY, maxX, maxY)      src/BarnesHutKernels.cu:152-195
+ *   keys       : uint32[n] SFC keys in body order       src/BarnesHutKernels.cu:197-240
+ *   sorted_idx : int32[n] permutation after the sort    src/BarnesHutKernels.cu:45
+ *   tree_keys  : uint64[n] tree-path keys in body order (the descent of src/BarnesHutKernels.cu:266-293)
+ * Any output pointer may be NULL. */
+int nb_bh_stages_host(nb_context* ctx, const float* pos, int n, int flags, float* bounds, uint32_t* keys,
+                      int32_t* sorted_idx, uint64_t* tree_keys);
+
+/* Canonical topology of the tree built by the last nb_bh_* call: one record per cell holding >= 2
+ * bodies, (prefix, level, count, mass, cx, cy) sorted by (prefix, level); prefix packs the path digits
+ * (x>=midX) + 2*(y>=midY) of src/BarnesHutKernels.cu:267-285 from bit 63 down.  Returns the number of
+ * records through *n_cells; call with NULL arrays to size the buffers (host memory). */
+int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* level, int32_t* count,
+                      double* mass, double* cx, double* cy);
+
+/* Counters of the last walk: nodes opened, children examined, lane interactions, max stack depth, nodes
+ * in the tree, status flags (bit 0 = stack overflow). */
+int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]);
+
+/* ---- Leapfrog kick/drift on a target slice (callers of the path) ------------ */
+
+/* The two kernels Verlet_DKD::integrate launches around computeAcceleration (src/IntegrationMethods.cu:
+ * 72-79 DKD_Verlet_1 and :81-93 DKD_Verlet_2), restricted to bodies [begin, begin+count).  `pos` is the
+ * full device float4[n] array (the slice is updated in place); `vel` and `acc` are slice-local
+ * float4[count].  Same mixed FP32/FP64 arithmetic as the reference (the 0.5 literal is a double). */
+int nb_verlet_dkd_drift(nb_context* ctx, float* pos, const float* vel, int begin, int count, float dt,
+                        void* stream);
+int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const float* acc, int begin, int count,
+                             float dt, void* stream);
+
+/* ---- calibration --------------------------------------------------------------------------------- */
+
+/* Measures this GPU's FP32 roofline denominators with register-resident microbenchmarks:
+ * out[0] = scalar FFMA TFLOP/s, out[1] = packed FFMA2 TFLOP/s, out[2] = MUFU.RSQ Gop/s,
+ * out[3] = SM clock in MHz derived from clock64 during the FFMA run. */
+int nb_calibrate(nb_context* ctx, double out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_B200_H */

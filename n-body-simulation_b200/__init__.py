@@ -1,0 +1,231 @@
+"""B200-native gravitational force engine -- Python host side.
+
+Mirrors the reference's compute plug-in surface (MoonArchitect/N-body-simulation,
+src/ComputeMethods.h:8-42, src/NbodySystem.h:12-43) on top of the C ABI in include/nbody_b200.h.
+All arithmetic happens in libnbody_b200.so (hand-written sm_100a CUDA); PyTorch is used only for
+device memory, streams and torch.distributed.  There is no CPU fallback: without the built library or
+without a B200 every compute call raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
+_lib = None
+
+NB_OK = 0
+NB_DIRECT_AUTO, NB_DIRECT_ORDERED = 0, 1
+NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS = 0, 1
+
+# every symbol include/nbody_b200.h declares (tests check that the library exports each one)
+ABI_SYMBOLS = [
+    "nb_create", "nb_destroy", "nb_last_error", "nb_device_info",
+    "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_last_launch",
+    "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
+    "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
+]
+
+
+class NbodyError(RuntimeError):
+    pass
+
+
+def library_path():
+    return _LIB_PATH
+
+
+def lib():
+    """Loads the C-ABI library.  Raises if it has not been built (no fallback path exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise NbodyError(f"{_LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(the engine has no CPU or PyTorch fallback)")
+        L = C.CDLL(_LIB_PATH)
+        vp, i, f = C.c_void_p, C.c_int, C.c_float
+        L.nb_create.argtypes = [C.POINTER(vp), i, i]
+        L.nb_destroy.argtypes = [vp]
+        L.nb_last_error.argtypes = [vp]
+        L.nb_last_error.restype = C.c_char_p
+        L.nb_device_info.argtypes = [vp, C.POINTER(i), C.POINTER(i), C.POINTER(C.c_uint64)]
+        L.nb_direct_accel.argtypes = [vp, vp, vp, i, i, f, i, vp]
+        L.nb_direct_accel_slice.argtypes = [vp, vp, i, i, i, vp, i, f, i, vp]
+        L.nb_direct_accel_host.argtypes = [vp, vp, vp, i, i, f, i]
+        L.nb_direct_last_launch.argtypes = [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i)]
+        L.nb_bh_accel.argtypes = [vp, vp, vp, i, f, f, i, vp]
+        L.nb_bh_accel_groups.argtypes = [vp, vp, vp, i, f, f, i, i, i, vp]
+        L.nb_bh_accel_host.argtypes = [vp, vp, vp, i, f, f, i]
+        L.nb_bh_stages_host.argtypes = [vp, vp, i, i, vp, vp, vp, vp]
+        L.nb_bh_export_tree.argtypes = [vp, C.POINTER(i), vp, vp, vp, vp, vp, vp]
+        L.nb_bh_last_counters.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.nb_calibrate.argtypes = [vp, C.POINTER(C.c_double)]
+        L.nb_verlet_dkd_drift.argtypes = [vp, vp, vp, i, i, f, vp]
+        L.nb_verlet_dkd_kick_drift.argtypes = [vp, vp, vp, vp, i, i, f, vp]
+        _lib = L
+    return _lib
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return C.c_void_p(stream)
+    return C.c_void_p(stream.cuda_stream)
+
+
+class Engine:
+    """Owner of one nb_context (scratch memory of one GPU)."""
+
+    def __init__(self, device=0, max_bodies=0):
+        self._h = C.c_void_p()
+        rc = lib().nb_create(C.byref(self._h), int(device), int(max_bodies))
+        if rc != NB_OK:
+            msg = lib().nb_last_error(None).decode()
+            self._h = None
+            raise NbodyError(f"nb_create failed ({rc}): {msg}")
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().nb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != NB_OK:
+            raise NbodyError(f"{what} failed ({rc}): {lib().nb_last_error(self._h).decode()}")
+
+    # -- direct ------------------------------------------------------------------------------------
+    def direct_accel(self, pos, acc, dim, softening, flags=NB_DIRECT_AUTO, stream=None):
+        """pos, acc: CUDA float32 tensors [n,4] (x,y,z,m) / (ax,ay,az,0)."""
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(acc, n)
+        self._check(lib().nb_direct_accel(self._h, pos.data_ptr(), acc.data_ptr(), n, dim, softening, flags,
+                                          _stream_ptr(stream)), "nb_direct_accel")
+
+    def direct_accel_slice(self, pos, target_begin, target_count, acc, dim, softening, flags=NB_DIRECT_AUTO,
+                           stream=None):
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(acc, target_count)
+        self._check(lib().nb_direct_accel_slice(self._h, pos.data_ptr(), n, target_begin, target_count,
+                                                acc.data_ptr(), dim, softening, flags, _stream_ptr(stream)),
+                    "nb_direct_accel_slice")
+
+    def direct_accel_host(self, pos, dim, softening, flags=NB_DIRECT_AUTO, out=None):
+        """pos: host float32 array/tensor [n,4]; returns host accelerations [n,4] (H2D + kernel + D2H)."""
+        p, n = _host_ptr(pos)
+        if out is None:
+            out = np.empty((n, 4), np.float32)
+        o, _ = _host_ptr(out)
+        self._check(lib().nb_direct_accel_host(self._h, p, o, n, dim, softening, flags), "nb_direct_accel_host")
+        return out
+
+    def direct_last_launch(self):
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        lib().nb_direct_last_launch(self._h, C.byref(a), C.byref(b), C.byref(c))
+        return dict(jsplit=a.value, blocks=b.value, launches=c.value)
+
+    # -- Barnes-Hut ----------------------------------------------------------------------------------
+    def bh_accel(self, pos, acc, theta, softening, flags=NB_BH_FRESH_BOUNDS, stream=None):
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(acc, n)
+        self._check(lib().nb_bh_accel(self._h, pos.data_ptr(), acc.data_ptr(), n, theta, softening, flags,
+                                      _stream_ptr(stream)), "nb_bh_accel")
+
+    def bh_accel_groups(self, pos, acc, theta, softening, group_begin, group_count, flags=NB_BH_FRESH_BOUNDS,
+                        stream=None):
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(acc, n)
+        self._check(lib().nb_bh_accel_groups(self._h, pos.data_ptr(), acc.data_ptr(), n, theta, softening, flags,
+                                             group_begin, group_count, _stream_ptr(stream)), "nb_bh_accel_groups")
+
+    def bh_accel_host(self, pos, theta, softening, flags=NB_BH_FRESH_BOUNDS, out=None):
+        p, n = _host_ptr(pos)
+        if out is None:
+            out = np.empty((n, 4), np.float32)
+        o, _ = _host_ptr(out)
+        self._check(lib().nb_bh_accel_host(self._h, p, o, n, theta, softening, flags), "nb_bh_accel_host")
+        return out
+
+    def bh_stages(self, pos, flags=NB_BH_FRESH_BOUNDS):
+        """Runs bounds -> keys -> sorts on device tensor `pos`; returns host arrays."""
+        n = pos.shape[0]
+        _check_tensor(pos, n)
+        bounds = np.zeros(4, np.float32)
+        keys = np.zeros(n, np.uint32)
+        sidx = np.zeros(n, np.int32)
+        tkeys = np.zeros(n, np.uint64)
+        self._check(lib().nb_bh_stages_host(self._h, pos.data_ptr(), n, flags, bounds.ctypes.data, keys.ctypes.data,
+                                            sidx.ctypes.data, tkeys.ctypes.data), "nb_bh_stages_host")
+        return dict(bounds=bounds, keys=keys, sorted_idx=sidx, tree_keys=tkeys)
+
+    def bh_export_tree(self):
+        k = C.c_int()
+        self._check(lib().nb_bh_export_tree(self._h, C.byref(k), None, None, None, None, None, None),
+                    "nb_bh_export_tree")
+        k = k.value
+        out = dict(prefix=np.zeros(k, np.uint64), level=np.zeros(k, np.int32), count=np.zeros(k, np.int32),
+                   mass=np.zeros(k, np.float64), cx=np.zeros(k, np.float64), cy=np.zeros(k, np.float64))
+        kk = C.c_int(k)
+        self._check(lib().nb_bh_export_tree(self._h, C.byref(kk), out["prefix"].ctypes.data, out["level"].ctypes.data,
+                                            out["count"].ctypes.data, out["mass"].ctypes.data, out["cx"].ctypes.data,
+                                            out["cy"].ctypes.data), "nb_bh_export_tree")
+        return out
+
+    def bh_last_counters(self):
+        c = (C.c_int64 * 6)()
+        self._check(lib().nb_bh_last_counters(self._h, c), "nb_bh_last_counters")
+        return dict(opened=c[0], examined=c[1], interactions=c[2], max_stack=c[3], nodes=c[4], status=c[5])
+
+    # -- Leapfrog (Verlet_DKD) kick/drift on a slice ---------------------------------------------------
+    def verlet_dkd_drift(self, pos, vel, begin, count, dt, stream=None):
+        self._check(lib().nb_verlet_dkd_drift(self._h, pos.data_ptr(), vel.data_ptr(), begin, count, dt,
+                                              _stream_ptr(stream)), "nb_verlet_dkd_drift")
+
+    def verlet_dkd_kick_drift(self, pos, vel, acc, begin, count, dt, stream=None):
+        self._check(lib().nb_verlet_dkd_kick_drift(self._h, pos.data_ptr(), vel.data_ptr(), acc.data_ptr(), begin,
+                                                   count, dt, _stream_ptr(stream)), "nb_verlet_dkd_kick_drift")
+
+    def calibrate(self):
+        out = (C.c_double * 4)()
+        self._check(lib().nb_calibrate(self._h, out), "nb_calibrate")
+        return dict(ffma_tflops=out[0], ffma2_tflops=out[1], mufu_gops=out[2], sm_mhz=out[3])
+
+    def device_info(self):
+        d, s, b = C.c_int(), C.c_int(), C.c_uint64()
+        lib().nb_device_info(self._h, C.byref(d), C.byref(s), C.byref(b))
+        return dict(device=d.value, sm_count=s.value, scratch_bytes=b.value)
+
+
+def _check_tensor(t, n):
+    import torch
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+            and t.dim() == 2 and t.shape[1] == 4 and t.shape[0] >= n):
+        raise NbodyError("expected a contiguous CUDA float32 tensor of shape [n, 4]")
+
+
+def _host_ptr(a):
+    try:
+        import torch
+        if isinstance(a, torch.Tensor):
+            if a.is_cuda or a.dtype != torch.float32 or not a.is_contiguous():
+                raise NbodyError("expected a contiguous host float32 tensor [n, 4]")
+            return C.c_void_p(a.data_ptr()), a.shape[0]
+    except ImportError:
+        pass
+    if not (isinstance(a, np.ndarray) and a.dtype == np.float32 and a.flags.c_contiguous and a.ndim == 2
+            and a.shape[1] == 4):
+        raise NbodyError("expected a contiguous host float32 array [n, 4]")
+    return C.c_void_p(a.ctypes.data), a.shape[0]
+
+
+from .system import R2, R3, ComputeMethods, NbodySystem  # noqa: E402,F401
+from . import ics  # noqa: E402,F401

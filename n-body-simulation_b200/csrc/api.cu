@@ -1,0 +1,111 @@
+// api.cu -- the extern "C" surface declared in include/nbody_b200.h (lifetime + direct path).
+#include "common.cuh"
+
+char g_nb_create_error[512] = {0};
+
+int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
+                     int dim, float softening, int flags, cudaStream_t stream);  // direct.cu
+void nb_bh_destroy(nb_context* ctx);                                              // bh.cu
+
+extern "C" {
+
+int nb_create(nb_context** out, int device, int max_bodies) {
+    if (!out) return nb_fail(nullptr, NB_ERR_INVALID, "nb_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return nb_fail(nullptr, NB_ERR_NO_DEVICE, "nb_create: no CUDA device (this engine has no CPU fallback)", e);
+    if (device < 0 || device >= count) return nb_fail(nullptr, NB_ERR_INVALID, "nb_create: device out of range");
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return nb_fail(nullptr, NB_ERR_CUDA, "cudaSetDevice", e);
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return nb_fail(nullptr, NB_ERR_CUDA, "cudaGetDeviceProperties", e);
+    if (prop.major != 10)
+        return nb_fail(nullptr, NB_ERR_NO_DEVICE, "nb_create: kernels are built for sm_100a only (need a B200)");
+    nb_context* ctx = new nb_context();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    e = cudaStreamCreateWithFlags(&ctx->host_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete ctx;
+        return nb_fail(nullptr, NB_ERR_CUDA, "cudaStreamCreate", e);
+    }
+    if (max_bodies > 0) {
+        size_t n_pad = ((size_t)max_bodies + 511) / 512 * 512;
+        int rc = nb_reserve(ctx, &ctx->packed, &ctx->packed_bytes, n_pad * 32);
+        if (rc) {
+            snprintf(g_nb_create_error, sizeof(g_nb_create_error), "%s", ctx->err);
+            delete ctx;
+            return rc;
+        }
+    }
+    *out = ctx;
+    return NB_OK;
+}
+
+int nb_destroy(nb_context* ctx) {
+    if (!ctx) return NB_OK;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    nb_bh_destroy(ctx);
+    if (ctx->packed) cudaFree(ctx->packed);
+    if (ctx->partial) cudaFree(ctx->partial);
+    if (ctx->dev_pos) cudaFree(ctx->dev_pos);
+    if (ctx->dev_acc) cudaFree(ctx->dev_acc);
+    if (ctx->host_stream) cudaStreamDestroy(ctx->host_stream);
+    delete ctx;
+    return NB_OK;
+}
+
+const char* nb_last_error(const nb_context* ctx) { return ctx ? ctx->err : g_nb_create_error; }
+
+int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* scratch_bytes) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (device) *device = ctx->device;
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (scratch_bytes) *scratch_bytes = ctx->packed_bytes + ctx->partial_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes;
+    return NB_OK;
+}
+
+int nb_direct_accel(nb_context* ctx, const float* pos, float* acc, int n, int dim, float softening, int flags,
+                    void* stream) {
+    return nb_direct_launch(ctx, pos, n, 0, n, acc, dim, softening, flags, (cudaStream_t)stream);
+}
+
+int nb_direct_accel_slice(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
+                          int dim, float softening, int flags, void* stream) {
+    return nb_direct_launch(ctx, pos, n, target_begin, target_count, acc, dim, softening, flags,
+                            (cudaStream_t)stream);
+}
+
+int nb_direct_accel_host(nb_context* ctx, const float* host_pos, float* host_acc, int n, int dim, float softening,
+                         int flags) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (n < 0 || (n > 0 && (!host_pos || !host_acc))) return nb_fail(ctx, NB_ERR_INVALID, "bad host buffers");
+    if (n == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    size_t bytes = (size_t)n * 16;
+    int rc = nb_reserve(ctx, &ctx->dev_pos, &ctx->dev_pos_bytes, bytes);
+    if (rc) return rc;
+    rc = nb_reserve(ctx, &ctx->dev_acc, &ctx->dev_acc_bytes, bytes);
+    if (rc) return rc;
+    cudaStream_t s = ctx->host_stream;
+    NB_CUDA(ctx, cudaMemcpyAsync(ctx->dev_pos, host_pos, bytes, cudaMemcpyHostToDevice, s));
+    rc = nb_direct_launch(ctx, (const float*)ctx->dev_pos, n, 0, n, (float*)ctx->dev_acc, dim, softening, flags, s);
+    if (rc) return rc;
+    NB_CUDA(ctx, cudaMemcpyAsync(host_acc, ctx->dev_acc, bytes, cudaMemcpyDeviceToHost, s));
+    NB_CUDA(ctx, cudaStreamSynchronize(s));
+    return NB_OK;
+}
+
+int nb_direct_last_launch(const nb_context* ctx, int* jsplit, int* blocks, int* launches) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (jsplit) *jsplit = ctx->last_jsplit;
+    if (blocks) *blocks = ctx->last_blocks;
+    if (launches) *launches = ctx->last_launches;
+    return NB_OK;
+}
+
+}  // extern "C"

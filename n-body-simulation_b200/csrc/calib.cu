@@ -1,0 +1,111 @@
+// calib.cu -- register-resident microbenchmarks that measure the FP32 roofline denominators of the GPU the
+// engine runs on (MEASURED_PEAKS.json carries only HBM and bf16 tensor peaks; the direct sum is bound by
+// the FP32 FMA pipe and, in 2D, the MUFU pipe -- SURVEY.md section 8d).
+#include "common.cuh"
+
+namespace {
+
+constexpr int CHAINS = 8;
+
+__global__ void __launch_bounds__(256) ffma_kernel(float* out, int iters, float a, float b, long long* cycles) {
+    float x[CHAINS];
+#pragma unroll
+    for (int k = 0; k < CHAINS; k++) x[k] = threadIdx.x * 1e-3f + k;
+    long long t0 = clock64();
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int k = 0; k < CHAINS; k++) x[k] = fmaf(x[k], a, b);
+    }
+    long long t1 = clock64();
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < CHAINS; k++) s += x[k];
+    if (s == 123.456f) out[0] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) cycles[0] = t1 - t0;
+}
+
+__global__ void __launch_bounds__(256) ffma2_kernel(float* out, int iters, float a, float b) {
+    uint64_t x[CHAINS];
+    const uint64_t A = pk2(a, a), B = pk2(b, b);
+#pragma unroll
+    for (int k = 0; k < CHAINS; k++) x[k] = pk2(threadIdx.x * 1e-3f + k, threadIdx.x * 2e-3f + k);
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int k = 0; k < CHAINS; k++) x[k] = fma2(x[k], A, B);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < CHAINS; k++) {
+        float lo, hi;
+        up2(x[k], lo, hi);
+        s += lo + hi;
+    }
+    if (s == 123.456f) out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) mufu_kernel(float* out, int iters) {
+    float x[CHAINS];
+#pragma unroll
+    for (int k = 0; k < CHAINS; k++) x[k] = 1.0f + threadIdx.x * 1e-3f + k;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int k = 0; k < CHAINS; k++) x[k] = rsqrt_approx(x[k]);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < CHAINS; k++) s += x[k];
+    if (s == 123.456f) out[0] = s;
+}
+
+}  // namespace
+
+extern "C" int nb_calibrate(nb_context* ctx, double out[4]) {
+    if (!ctx || !out) return NB_ERR_INVALID;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    float* d_out = nullptr;
+    long long* d_cyc = nullptr;
+    NB_CUDA(ctx, cudaMalloc(&d_out, 16));
+    NB_CUDA(ctx, cudaMalloc(&d_cyc, 16));
+    cudaEvent_t e0, e1;
+    NB_CUDA(ctx, cudaEventCreate(&e0));
+    NB_CUDA(ctx, cudaEventCreate(&e1));
+    const int blocks = ctx->sm_count * 8, threads = 256;
+    const double lanes = (double)blocks * threads;
+    float ms = 0.f;
+    auto timeit = [&](int which, int iters) -> float {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; rep++) {  // first rep is the warm-up
+            cudaEventRecord(e0, 0);
+            if (which == 0) ffma_kernel<<<blocks, threads>>>(d_out, iters, 1.0001f, 0.5f, d_cyc);
+            else if (which == 1) ffma2_kernel<<<blocks, threads>>>(d_out, iters, 1.0001f, 0.5f);
+            else mufu_kernel<<<blocks, threads>>>(d_out, iters);
+            cudaEventRecord(e1, 0);
+            cudaEventSynchronize(e1);
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0 && ms < best) best = ms;
+        }
+        return best;
+    };
+    const int it_f = 8192, it_m = 1024;
+    float t_ffma = timeit(0, it_f);
+    long long cyc = 0;
+    NB_CUDA(ctx, cudaMemcpy(&cyc, d_cyc, sizeof(cyc), cudaMemcpyDeviceToHost));
+    float t_ffma2 = timeit(1, it_f);
+    float t_mufu = timeit(2, it_m);
+    NB_CUDA(ctx, cudaGetLastError());
+    out[0] = lanes * it_f * 8.0 * CHAINS * 2.0 / (t_ffma * 1e-3) / 1e12;
+    out[1] = lanes * it_f * 8.0 * CHAINS * 4.0 / (t_ffma2 * 1e-3) / 1e12;
+    out[2] = lanes * it_m * 8.0 * CHAINS / (t_mufu * 1e-3) / 1e9;
+    out[3] = (double)cyc / (t_ffma * 1e-3) / 1e6;  // block 0 runs ~ the whole kernel (8 CTAs/SM resident at once)
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    cudaFree(d_cyc);
+    return NB_OK;
+}

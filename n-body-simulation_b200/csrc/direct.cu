@@ -1,0 +1,270 @@
+// direct.cu -- all-pairs softened gravity for sm_100a.
+//
+// Replaces direct2DComputeKernel / direct3DComputeKernel (reference src/DirectComputeKernels.cu:10-37,46-75).
+// Same per-interaction arithmetic as the reference (so that NB_DIRECT_ORDERED reproduces it bit for bit):
+//     d   = s_j - b_i                                  (:61-63)
+//     r2  = fma(dz,dz, fma(dy,dy, fma(dx,dx, eps)))    (:64, contracted left to right)
+//     inv = MUFU.RSQ(r2)                               (:65)
+//     s   = ((inv*inv)*inv)*m_j   [2D: (inv*inv)*m_j]  (:66 / :28)
+//     a  += d*s  (fma)                                 (:67)
+// What is different is everything around it:
+//   * FP32x2 packed math (FADD2/FFMA2/FMUL2): one instruction serves two targets of the same thread, so the
+//     12 FP32-pipe operations of an interaction cost 6 issue slots and the FMA pipe, not the scheduler, is
+//     the limit.  The source operand of a packed op must be a register pair holding the same value twice;
+//     sources are therefore pre-packed once per evaluation into 32-byte records {x,x,y,y | z,z,m,m}.
+//   * each thread owns 2*PAIRS targets in registers; one pair of broadcast LDS.128 serves all of them.
+//   * source tiles stream into shared memory with cp.async.bulk (TMA, UBLKCP) into a 3-stage ring guarded
+//     by mbarriers; no __syncthreads in the main loop.
+//   * the source range can be split over blockIdx.y (partials reduced in fixed order -> deterministic) so
+//     that small target counts (N = 16,384; an 1/8 slice of 1M on 8 GPUs) still fill 148 SMs.
+#include "common.cuh"
+
+namespace {
+
+constexpr int NT = 256;      // threads per CTA
+constexpr int TILE = 512;    // sources per pipeline stage (16 KB)
+constexpr int STAGES = 3;
+constexpr int REC_BYTES = 32;
+constexpr int SMEM_BYTES = STAGES * TILE * REC_BYTES + 2 * STAGES * 8;
+
+__global__ void pack_sources_kernel(const float4* __restrict__ pos, int n, int n_pad, float4* __restrict__ packed) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);  // padding: massless body at the origin adds exactly 0
+    if (i < n) p = pos[i];
+    packed[2 * (size_t)i] = make_float4(p.x, p.x, p.y, p.y);
+    packed[2 * (size_t)i + 1] = make_float4(p.z, p.z, p.w, p.w);
+}
+
+template <int DIM, int PAIRS, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+direct_kernel(const float4* __restrict__ pos,     // all bodies (targets are read from here)
+              const float4* __restrict__ packed,  // duplicated sources, ntiles*TILE records
+              int ntiles, int target_begin, int target_count, float eps,
+              float4* __restrict__ out,           // acc (jsplit == 1) or partial sums [jsplit][target_count]
+              int jsplit) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const ulonglong2* tiles = reinterpret_cast<const ulonglong2*>(smem);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * TILE * REC_BYTES);
+    uint64_t* empty = full + STAGES;
+
+    const int tid = threadIdx.x;
+    const int js = blockIdx.y;
+    const int tile0 = (int)((long long)ntiles * js / jsplit);
+    const int tile1 = (int)((long long)ntiles * (js + 1) / jsplit);
+    const int my_tiles = tile1 - tile0;
+
+    // targets: thread owns slice-local ids base + k*NT + tid, k < 2*PAIRS (coalesced loads / stores)
+    const int base = blockIdx.x * (NT * 2 * PAIRS);
+    uint64_t BX[PAIRS], BY[PAIRS], BZ[PAIRS];
+    uint64_t AX[PAIRS], AY[PAIRS], AZ[PAIRS];
+#pragma unroll
+    for (int p = 0; p < PAIRS; p++) {
+        int i0 = min(base + (2 * p) * NT + tid, target_count - 1);
+        int i1 = min(base + (2 * p + 1) * NT + tid, target_count - 1);
+        float4 t0 = pos[target_begin + i0];
+        float4 t1 = pos[target_begin + i1];
+        BX[p] = pk2(t0.x, t1.x);
+        BY[p] = pk2(t0.y, t1.y);
+        BZ[p] = pk2(t0.z, t1.z);
+        AX[p] = AY[p] = AZ[p] = 0ull;  // (+0.f, +0.f)
+    }
+    const uint64_t E2 = pk2(eps, eps);
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], NT / 32);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const int pre = my_tiles < STAGES ? my_tiles : STAGES;
+        for (int s = 0; s < pre; s++) {
+            mbar_expect_tx(&full[s], TILE * REC_BYTES);
+            bulk_g2s(smem + s * TILE * REC_BYTES, packed + 2 * (size_t)(tile0 + s) * TILE, TILE * REC_BYTES, &full[s]);
+        }
+    }
+
+    for (int it = 0; it < my_tiles; it++) {
+        const int s = it % STAGES;
+        mbar_wait(&full[s], (it / STAGES) & 1);
+        const ulonglong2* tp = tiles + s * (TILE * 2);
+#pragma unroll 2
+        for (int j = 0; j < TILE; j++) {
+            const ulonglong2 a = tp[2 * j];      // (x,x) (y,y)
+            const ulonglong2 b = tp[2 * j + 1];  // (z,z) (m,m)
+#pragma unroll
+            for (int p = 0; p < PAIRS; p++) {
+                uint64_t dx = sub2(a.x, BX[p]);
+                uint64_t dy = sub2(a.y, BY[p]);
+                uint64_t r2 = fma2(dx, dx, E2);
+                r2 = fma2(dy, dy, r2);
+                uint64_t dz;
+                if (DIM == 3) {
+                    dz = sub2(b.x, BZ[p]);
+                    r2 = fma2(dz, dz, r2);
+                }
+                float r0, r1;
+                up2(r2, r0, r1);
+                uint64_t inv = pk2(rsqrt_approx(r0), rsqrt_approx(r1));
+                uint64_t sc = mul2(inv, inv);
+                if (DIM == 3) sc = mul2(sc, inv);
+                sc = mul2(sc, b.y);
+                AX[p] = fma2(dx, sc, AX[p]);
+                AY[p] = fma2(dy, sc, AY[p]);
+                if (DIM == 3) AZ[p] = fma2(dz, sc, AZ[p]);
+            }
+        }
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+        // refill the stage consumed one iteration ago (every warp has had a whole tile of time to leave it)
+        if (tid == 0 && it >= 1) {
+            const int prev = it - 1;
+            const int nxt = prev + STAGES;
+            if (nxt < my_tiles) {
+                const int sp = prev % STAGES;
+                mbar_wait(&empty[sp], (prev / STAGES) & 1);
+                mbar_expect_tx(&full[sp], TILE * REC_BYTES);
+                bulk_g2s(smem + sp * TILE * REC_BYTES, packed + 2 * (size_t)(tile0 + nxt) * TILE, TILE * REC_BYTES,
+                         &full[sp]);
+            }
+        }
+    }
+
+    float4* dst = out + (size_t)js * target_count;
+#pragma unroll
+    for (int p = 0; p < PAIRS; p++) {
+        float x0, x1, y0, y1, z0 = 0.f, z1 = 0.f;
+        up2(AX[p], x0, x1);
+        up2(AY[p], y0, y1);
+        if (DIM == 3) up2(AZ[p], z0, z1);
+        int i0 = base + (2 * p) * NT + tid;
+        int i1 = base + (2 * p + 1) * NT + tid;
+        if (i0 < target_count) dst[i0] = make_float4(x0, y0, z0, 0.f);
+        if (i1 < target_count) dst[i1] = make_float4(x1, y1, z1, 0.f);
+    }
+}
+
+// acc[i] = partial[0][i] + partial[1][i] + ... in that order (deterministic).
+__global__ void reduce_partials_kernel(const float4* __restrict__ partial, int target_count, int jsplit,
+                                       float4* __restrict__ acc) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= target_count) return;
+    float4 s = partial[i];
+    for (int k = 1; k < jsplit; k++) {
+        float4 v = partial[(size_t)k * target_count + i];
+        s.x += v.x;
+        s.y += v.y;
+        s.z += v.z;
+    }
+    s.w = 0.f;
+    acc[i] = s;
+}
+
+__global__ void zero_acc_kernel(float4* acc, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+using kernel_fn = void (*)(const float4*, const float4*, int, int, int, float, float4*, int);
+
+struct Variant {
+    kernel_fn fn;
+    int pairs;
+    int occupancy;  // resident CTAs per SM, filled lazily
+};
+
+Variant g_variants[2][2] = {
+    {{direct_kernel<2, 2, 3>, 2, 0}, {direct_kernel<2, 4, 2>, 4, 0}},
+    {{direct_kernel<3, 2, 3>, 2, 0}, {direct_kernel<3, 4, 2>, 4, 0}},
+};
+
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+}  // namespace
+
+int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
+                     int dim, float softening, int flags, cudaStream_t stream) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
+    if (n < 0 || target_begin < 0 || target_count < 0 || (long long)target_begin + target_count > n)
+        return nb_fail(ctx, NB_ERR_INVALID, "target slice outside [0, n)");
+    if (target_count == 0) return NB_OK;
+    if (!pos || !acc) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    const int ntiles = (n + TILE - 1) / TILE;
+    const int n_pad = ntiles * TILE;
+    int rc = nb_reserve(ctx, &ctx->packed, &ctx->packed_bytes, (size_t)n_pad * REC_BYTES);
+    if (rc) return rc;
+
+    // choose the register blocking: 8 targets/thread when there are enough targets to fill the GPU with
+    // them, else 4 (finer granularity); NB_DIRECT_PAIRS overrides for tuning.
+    int pairs = env_int("NB_DIRECT_PAIRS", 0);
+    if (pairs != 2 && pairs != 4) pairs = (target_count >= ctx->sm_count * 2 * NT * 8) ? 4 : 2;
+    Variant& v = g_variants[dim - 2][pairs == 4 ? 1 : 0];
+    if (v.occupancy == 0) {
+        NB_CUDA(ctx, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        int occ = 0;
+        NB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, NT, SMEM_BYTES));
+        v.occupancy = occ > 0 ? occ : 1;
+    }
+    const int per_block = NT * 2 * v.pairs;
+    const int tblocks = (target_count + per_block - 1) / per_block;
+    const int slots = ctx->sm_count * v.occupancy;
+
+    // split the source range so that the grid is close to a whole number of waves
+    int jsplit = 1;
+    if (!(flags & NB_DIRECT_ORDERED)) {
+        int forced = env_int("NB_DIRECT_JSPLIT", 0);
+        if (forced > 0) {
+            jsplit = forced < ntiles ? forced : ntiles;
+        } else {
+            int max_js = ntiles / 4;  // keep >= 4 tiles (2048 sources) per CTA
+            if (max_js > 64) max_js = 64;
+            if (max_js < 1) max_js = 1;
+            double best = -1.0;
+            for (int js = 1; js <= max_js; js++) {
+                long long blocks = (long long)tblocks * js;
+                long long waves = (blocks + slots - 1) / slots;
+                double eff = (double)blocks / (double)(waves * slots);
+                if (eff > best + 1e-9) {
+                    best = eff;
+                    jsplit = js;
+                }
+                if (eff >= 0.97) break;
+            }
+        }
+    }
+    if (jsplit < 1) jsplit = 1;
+
+    float4* out = reinterpret_cast<float4*>(acc);
+    if (jsplit > 1) {
+        rc = nb_reserve(ctx, &ctx->partial, &ctx->partial_bytes, (size_t)jsplit * target_count * sizeof(float4));
+        if (rc) return rc;
+        out = reinterpret_cast<float4*>(ctx->partial);
+    }
+
+    pack_sources_kernel<<<(n_pad + 255) / 256, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, n_pad,
+                                                                 reinterpret_cast<float4*>(ctx->packed));
+    dim3 grid(tblocks, jsplit);
+    v.fn<<<grid, NT, SMEM_BYTES, stream>>>(reinterpret_cast<const float4*>(pos),
+                                           reinterpret_cast<const float4*>(ctx->packed), ntiles, target_begin,
+                                           target_count, softening, out, jsplit);
+    int launches = 2;
+    if (jsplit > 1) {
+        reduce_partials_kernel<<<(target_count + 255) / 256, 256, 0, stream>>>(
+            reinterpret_cast<const float4*>(ctx->partial), target_count, jsplit, reinterpret_cast<float4*>(acc));
+        launches = 3;
+    }
+    NB_CUDA(ctx, cudaGetLastError());
+    ctx->last_jsplit = jsplit;
+    ctx->last_blocks = tblocks * jsplit;
+    ctx->last_launches = launches;
+    return NB_OK;
+}

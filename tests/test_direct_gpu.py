@@ -1,0 +1,137 @@
+"""GPU parity tests of the direct all-pairs path, through the C ABI (include/nbody_b200.h)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+EPS = 1.01
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _rel(a, b, d):
+    return np.linalg.norm(a[:, :d].astype(np.float64) - b[:, :d], axis=1) / np.linalg.norm(b[:, :d], axis=1)
+
+
+def _run(engine, pos_h, dim, flags=0):
+    import torch
+    pos = torch.from_numpy(pos_h).cuda()
+    acc = torch.full((pos_h.shape[0], 4), 7.0, device="cuda")  # poison: every entry must be overwritten
+    engine.direct_accel(pos, acc, dim, EPS, flags)
+    torch.cuda.synchronize()
+    return acc.cpu().numpy()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("n", [1, 2, 31, 128, 513, 1000, 4096, 16384])
+def test_direct_vs_fp64_oracle(engine, pkg, oracle, n, dim):
+    """Tolerance: 1e-5 relative (BASELINE.json north_star) on the field norm and on the median body; the
+    worst body is allowed 5e-5 because FP32 summation of N terms alone moves the reference's own kernel
+    that far from FP64 (measured: oracle_direct_f32 vs f64 max 1.3e-5 at N=16384)."""
+    pos = pkg.ics.uniform_disk(n, seed=11, z_half_height=3000.0 if dim == 3 else 0.0)
+    got = _run(engine, pos, dim)
+    ref = oracle.direct_f64(pos, dim, EPS)
+    assert np.all(got[:, 3] == 0) and (dim == 3 or np.all(got[:, 2] == 0))
+    if n == 1:
+        assert np.all(got == 0)
+        return
+    field = np.linalg.norm(got[:, :dim] - ref[:, :dim]) / np.linalg.norm(ref[:, :dim])
+    e = _rel(got, ref, dim)
+    assert field < 1e-5 and np.median(e) < 1e-5 and e.max() < 5e-5, (field, np.median(e), e.max())
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_direct_ordered_matches_f32_oracle(engine, pkg, oracle, dim):
+    """NB_DIRECT_ORDERED sums sources in index order with one accumulator, like the reference kernel and
+    like oracle_direct_f32; the only difference left is MUFU.RSQ vs 1/sqrtf (about 1 ulp per term)."""
+    n = 3000
+    pos = pkg.ics.uniform_disk(n, seed=12, z_half_height=3000.0 if dim == 3 else 0.0)
+    got = _run(engine, pos, dim, pkg.NB_DIRECT_ORDERED)
+    assert engine.direct_last_launch()["jsplit"] == 1
+    o32 = oracle.direct_f32(pos, dim, EPS)
+    e = _rel(got, o32.astype(np.float64), dim)
+    assert e.max() < 5e-6, e.max()
+
+
+@pytest.mark.parametrize("name", ["direct2d_n2048", "direct3d_n2048", "direct3d_n16384"])
+def test_direct_matches_reference_golden(engine, pkg, name):
+    """Golden outputs of the reference's own CUDA kernels (tests/golden/make_ref_golden.py).  Ordered mode
+    must reproduce them bit for bit; the default (split) mode within 1e-5 of the field norm."""
+    path = os.path.join(ROOT, "tests", "golden", name + ".npz")
+    if not os.path.exists(path):
+        pytest.skip("golden fixture not generated yet")
+    g = np.load(path)
+    dim = int(g["dim"])
+    got = _run(engine, g["pos"], dim, pkg.NB_DIRECT_ORDERED)
+    assert np.array_equal(got[:, :dim], g["acc"]), np.abs(got[:, :dim] - g["acc"]).max()
+    got2 = _run(engine, g["pos"], dim)
+    field = np.linalg.norm(got2[:, :dim].astype(np.float64) - g["acc"]) / np.linalg.norm(g["acc"].astype(np.float64))
+    assert field < 1e-5, field
+
+
+def test_direct_matches_reference_kernels_live(engine, pkg):
+    """When oracle/_ref/libnbody_ref.so travelled to the box: run the reference kernel and ours on the same
+    device buffers; ordered mode is bit-identical."""
+    import torch
+    so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
+    if not os.path.exists(so):
+        pytest.skip("oracle/_ref not built")
+    ref = C.CDLL(so)
+    ref.ref_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float]
+    for dim, n in ((2, 4096), (3, 8192)):
+        pos_h = pkg.ics.uniform_disk(n, seed=13, z_half_height=3000.0 if dim == 3 else 0.0)
+        pos = torch.from_numpy(pos_h).cuda()
+        a_ref = torch.zeros(n, 4, device="cuda")
+        assert ref.ref_direct(pos.data_ptr(), a_ref.data_ptr(), n, dim, EPS) == 0
+        torch.cuda.synchronize()
+        got = _run(engine, pos_h, dim, pkg.NB_DIRECT_ORDERED)
+        assert np.array_equal(got[:, :dim], a_ref.cpu().numpy()[:, :dim])
+
+
+def test_direct_slices_tile_the_full_result(engine, pkg):
+    """Target slices (the multi-GPU decomposition) reproduce the full evaluation exactly when both use the
+    ordered mode, for ragged slice boundaries."""
+    import torch
+    n = 5000
+    pos_h = pkg.ics.uniform_disk(n, seed=14, z_half_height=3000.0)
+    full = _run(engine, pos_h, 3, pkg.NB_DIRECT_ORDERED)
+    pos = torch.from_numpy(pos_h).cuda()
+    cuts = [0, 1, 777, 2048, 4999, 5000]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        acc = torch.zeros(b - a, 4, device="cuda")
+        engine.direct_accel_slice(pos, a, b - a, acc, 3, EPS, pkg.NB_DIRECT_ORDERED)
+        torch.cuda.synchronize()
+        assert np.array_equal(acc.cpu().numpy(), full[a:b])
+
+
+def test_direct_split_is_deterministic_and_linear_in_mass(engine, pkg):
+    """Size-independent properties at a larger N: two runs are bit-identical (no atomics), and doubling
+    every mass doubles every acceleration exactly (power-of-two scaling commutes with rounding)."""
+    n = 65536
+    pos = pkg.ics.uniform_disk(n, seed=15, z_half_height=3000.0)
+    a1 = _run(engine, pos, 3)
+    assert engine.direct_last_launch()["jsplit"] > 1
+    a2 = _run(engine, pos, 3)
+    assert np.array_equal(a1, a2)
+    pos2 = pos.copy()
+    pos2[:, 3] *= 2
+    a3 = _run(engine, pos2, 3)
+    assert np.array_equal(a3, 2 * a1)
+
+
+def test_direct_host_entry_point(engine, pkg, oracle):
+    pos = pkg.ics.uniform_disk(2048, seed=16, z_half_height=3000.0)
+    got = engine.direct_accel_host(pos, 3, EPS)
+    ref = oracle.direct_f64(pos, 3, EPS)
+    assert _rel(got, ref, 3).max() < 5e-5
+
+
+def test_bad_arguments_are_rejected(engine, pkg):
+    import torch
+    pos = torch.zeros(16, 4, device="cuda")
+    acc = torch.zeros(16, 4, device="cuda")
+    with pytest.raises(pkg.NbodyError):
+        engine.direct_accel(pos, acc, 4, EPS)
+    with pytest.raises(pkg.NbodyError):
+        engine.direct_accel_slice(pos, 10, 10, acc, 3, EPS)

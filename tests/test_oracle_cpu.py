@@ -1,0 +1,183 @@
+"""CPU tests: the oracle against the golden fixtures produced by the reference's CUDA kernels, oracle
+self-consistency, and the C-ABI library's exported surface.  No GPU needed."""
+import ctypes as C
+import glob
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+EPS = 1.01
+
+
+def _gold(name):
+    p = os.path.join(GOLD, name + ".npz")
+    if not os.path.exists(p):
+        pytest.skip(f"{name}.npz not generated yet")
+    return np.load(p)
+
+
+@pytest.mark.parametrize("name", ["direct2d_n2048", "direct3d_n2048", "direct3d_n16384"])
+def test_oracle_direct_against_reference_golden(oracle, name):
+    """oracle_direct_f32 restates the reference kernel up to MUFU.RSQ vs 1/sqrtf: <= 2e-6 of |a| per body."""
+    g = _gold(name)
+    dim = int(g["dim"])
+    o32 = oracle.direct_f32(g["pos"], dim, float(g["eps"]))
+    ref = g["acc"].astype(np.float64)
+    e = np.linalg.norm(o32[:, :dim] - ref, axis=1) / np.linalg.norm(ref, axis=1)
+    assert e.max() < 5e-6, e.max()
+    o64 = oracle.direct_f64(g["pos"], dim, float(g["eps"]))
+    field = np.linalg.norm(o64[:, :dim] - ref) / np.linalg.norm(ref)
+    assert field < 1e-5, field
+
+
+def test_oracle_direct_variants_agree(oracle, pkg):
+    pos = pkg.ics.uniform_disk(1500, seed=3, z_half_height=3000.0)
+    for dim in (2, 3):
+        a = oracle.direct_f32(pos, dim, EPS)
+        b = oracle.direct_f32(pos, dim, EPS, fast=True)
+        c = oracle.direct_f64(pos, dim, EPS)
+        na = np.linalg.norm(c[:, :dim], axis=1)
+        assert (np.linalg.norm(a[:, :dim] - c[:, :dim], axis=1) / na).max() < 2e-5
+        assert (np.linalg.norm(b[:, :dim] - c[:, :dim], axis=1) / na).max() < 2e-5
+        # target slices tile the full result
+        s = oracle.direct_f32(pos, dim, EPS, t0=100, nt=300)
+        assert np.array_equal(s, a[100:400])
+
+
+def test_oracle_direct_force_laws(oracle):
+    """Two bodies: 3D a = m d / (eps + r^2)^(3/2), 2D a = m d / (eps + r^2)."""
+    pos = np.array([[0, 0, 0, 5.0], [3, 4, 0, 7.0]], np.float32)
+    a3 = oracle.direct_f64(pos, 3, 0.25)
+    a2 = oracle.direct_f64(pos, 2, 0.25)
+    r2 = 25.25
+    assert np.allclose(a3[0], 7.0 * np.array([3, 4, 0]) / r2 ** 1.5)
+    assert np.allclose(a2[0, :2], 7.0 * np.array([3, 4]) / r2)
+    assert np.allclose(a3[1], -5.0 * np.array([3, 4, 0]) / r2 ** 1.5)
+
+
+@pytest.mark.parametrize("name", ["bh_disk_n8192", "bh_disk_n16384_t04", "bh_clustered_n8192"])
+def test_oracle_bh_integer_stages_against_reference_golden(oracle, name):
+    """Bounds, SFC keys, sort permutation and tree topology of the oracle are bit-exact against the
+    reference's kernels (BASELINE.json north_star)."""
+    g = _gold(name)
+    pos = g["pos"]
+    b = oracle.bh_bounds(pos)
+    assert np.array_equal(b, g["bounds"])
+    k = oracle.bh_keys(pos, b)
+    sk, si = oracle.sort_pairs(k)
+    assert np.array_equal(sk, g["sorted_keys"])
+    assert np.array_equal(si, g["sorted_idx"])
+    t = oracle.Tree(pos, b, si)
+    c = t.canonical()
+    assert int(g["n_in_tree"]) == pos.shape[0]
+    assert np.array_equal(c["prefix"], g["cell_prefix"])
+    assert np.array_equal(c["level"], g["cell_level"])
+    assert np.array_equal(c["count"], g["cell_count"])
+    # monopoles: the reference accumulates with float atomics in scheduler order -> 1e-5, not bit-wise
+    assert np.allclose(c["mass"], g["cell_mass"], rtol=1e-5)
+    scale = np.abs(g["pos"][:, :2]).max()
+    assert np.abs(c["cx"] - g["cell_cx"]).max() < 2e-5 * scale
+    assert np.abs(c["cy"] - g["cell_cy"]).max() < 2e-5 * scale
+
+
+@pytest.mark.parametrize("name", ["bh_disk_n8192", "bh_disk_n16384_t04", "bh_clustered_n8192"])
+def test_oracle_bh_accelerations_against_reference_golden(oracle, name):
+    """The oracle walk (prebuilt top tree emulated) reproduces the reference's accelerations up to the
+    reference's nondeterministic float-atomic centre-of-mass sums: median 1e-6, 99 % of bodies 1e-4."""
+    g = _gold(name)
+    pos = g["pos"]
+    b = oracle.bh_bounds(pos)
+    _, si = oracle.sort_pairs(oracle.bh_keys(pos, b))
+    t = oracle.Tree(pos, b, si, prebuilt=True)
+    acc, _ = t.walk(si, float(g["theta"]), float(g["eps"]))
+    ref = g["acc"].astype(np.float64)
+    e = np.linalg.norm(acc[:, :2] - ref, axis=1) / np.linalg.norm(ref, axis=1)
+    assert np.median(e) < 5e-6 and np.quantile(e, 0.99) < 1e-3, (np.median(e), np.quantile(e, 0.99), e.max())
+
+
+def test_oracle_bh_converges_to_direct_sum(oracle, pkg):
+    """theta -> 0 opens every cell: the walk equals the 2D direct sum to rounding; theta = 0.5 stays within
+    a percent-level error distribution."""
+    pos = pkg.ics.uniform_disk(4096, seed=21)
+    d = oracle.direct_f64(pos, 2, EPS)
+    r = oracle.bh_accel(pos, 1e-4, EPS)
+    e = np.linalg.norm(r["acc"][:, :2] - d[:, :2], axis=1) / np.linalg.norm(d[:, :2], axis=1)
+    assert e.max() < 5e-5
+    r = oracle.bh_accel(pos, 0.5, EPS)
+    e = np.linalg.norm(r["acc"][:, :2] - d[:, :2], axis=1) / np.linalg.norm(d[:, :2], axis=1)
+    assert np.median(e) < 2e-3 and e.max() < 0.1
+    assert r["counters"]["interactions"] < 0.5 * 4096 * 4096
+
+
+def test_oracle_keys_and_sort(oracle, pkg):
+    pos = pkg.ics.uniform_disk(5000, seed=22)
+    b = oracle.bh_bounds(pos)
+    k = oracle.bh_keys(pos, b)
+    sk, si = oracle.sort_pairs(k)
+    order = np.argsort(k, kind="stable")
+    assert np.array_equal(si, order.astype(np.int32)) and np.array_equal(sk, k[order])
+    tk = oracle.bh_tree_keys(pos, b)
+    stk, sti = oracle.sort_pairs(tk)
+    order = np.argsort(tk, kind="stable")
+    assert np.array_equal(sti, order.astype(np.int32))
+    # away from exact midpoint hits the first 16 levels of the tree key equal the SFC key
+    assert np.mean((tk >> np.uint64(32)).astype(np.uint32) == k) > 0.99
+
+
+def test_oracle_tree_handles_duplicates_and_tiny_inputs(oracle):
+    pos = np.zeros((6, 4), np.float32)
+    pos[:, 3] = 1
+    pos[:3, :2] = [[1, 1], [1, 1], [1, 1]]          # three coincident bodies -> depth-cap bucket
+    pos[3:, :2] = [[-5, 2], [4, -3], [0, 0]]
+    b = oracle.bh_bounds(pos)
+    _, si = oracle.sort_pairs(oracle.bh_keys(pos, b))
+    t = oracle.Tree(pos, b, si)
+    c = t.canonical()
+    assert c["level"].max() == 32 and c["count"][c["level"] == 32][0] == 3
+    acc, _ = t.walk(si, 0.5, EPS)
+    d = oracle.direct_f64(pos, 2, EPS)
+    assert np.allclose(acc[:, :2], d[:, :2], rtol=1e-4, atol=1e-7)
+    one = np.array([[1, 2, 0, 3]], np.float32)
+    r = oracle.bh_accel(one, 0.5, EPS)
+    assert np.all(r["acc"] == 0)
+
+
+# ---- the C-ABI library -------------------------------------------------------------------------------
+
+def test_header_symbols_are_exported(pkg):
+    """Every function include/nbody_b200.h declares is exported by libnbody_b200.so (load only, no compute)."""
+    hdr = open(os.path.join(ROOT, "include", "nbody_b200.h")).read()
+    declared = set(re.findall(r"^\s*(?:int|const char\*)\s+(nb_\w+)\s*\(", hdr, flags=re.M))
+    assert declared == set(pkg.ABI_SYMBOLS), declared ^ set(pkg.ABI_SYMBOLS)
+    L = C.CDLL(pkg.library_path())
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_no_gpu_means_loud_failure(pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(pkg.NbodyError, match="no CUDA device"):
+        pkg.Engine(0)
+
+
+def test_product_never_touches_the_oracle():
+    """The product package must not import, link or execute anything under oracle/."""
+    for path in glob.glob(os.path.join(ROOT, "n-body-simulation_b200", "**", "*"), recursive=True):
+        if os.path.isfile(path) and path.endswith((".py", ".cu", ".cuh", ".cpp", ".h", "Makefile")):
+            txt = open(path, errors="ignore").read()
+            assert "liboracle" not in txt and "import oracle" not in txt and "from oracle" not in txt, path
+
+
+def test_ics_are_reproducible(pkg):
+    a = pkg.ics.uniform_disk(1000, seed=1)
+    b = pkg.ics.uniform_disk(1000, seed=1)
+    assert np.array_equal(a, b) and a[0, 3] == 10000 and np.all(a[1:, 3] == 70000)
+    r = np.hypot(a[1:, 0], a[1:, 1])
+    assert r.min() >= 0.02 * 30000 * 0.999 and r.max() <= 30000
+    assert not np.array_equal(a, pkg.ics.uniform_disk(1000, seed=2))
