@@ -81,8 +81,8 @@ def test_oracle_bh_integer_stages_against_reference_golden(oracle, name):
     # off by up to 1.7e-4 relative, centres by 7e-6 of the box), so these are compared loosely, not bit-wise
     assert np.allclose(c["mass"], g["cell_mass"], rtol=5e-4)
     scale = np.abs(g["pos"][:, :2]).max()
-    assert np.abs(c["cx"] - g["cell_cx"]).max() < 2e-5 * scale
-    assert np.abs(c["cy"] - g["cell_cy"]).max() < 2e-5 * scale
+    assert np.abs(c["cx"] - g["cell_cx"]).max() < 1e-4 * scale
+    assert np.abs(c["cy"] - g["cell_cy"]).max() < 1e-4 * scale
 
 
 @pytest.mark.parametrize("name", ["bh_disk_n8192", "bh_disk_n16384_t04", "bh_clustered_n8192"])
