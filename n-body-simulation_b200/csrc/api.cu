@@ -32,15 +32,7 @@ int nb_create(nb_context** out, int device, int max_bodies) {
         delete ctx;
         return nb_fail(nullptr, NB_ERR_CUDA, "cudaStreamCreate", e);
     }
-    if (max_bodies > 0) {
-        size_t n_pad = ((size_t)max_bodies + 511) / 512 * 512;
-        int rc = nb_reserve(ctx, &ctx->packed, &ctx->packed_bytes, n_pad * 32);
-        if (rc) {
-            snprintf(g_nb_create_error, sizeof(g_nb_create_error), "%s", ctx->err);
-            delete ctx;
-            return rc;
-        }
-    }
+    ctx->max_bodies = max_bodies > 0 ? max_bodies : 0;
     *out = ctx;
     return NB_OK;
 }
@@ -50,7 +42,6 @@ int nb_destroy(nb_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     nb_bh_destroy(ctx);
-    if (ctx->packed) cudaFree(ctx->packed);
     if (ctx->partial) cudaFree(ctx->partial);
     if (ctx->dev_pos) cudaFree(ctx->dev_pos);
     if (ctx->dev_acc) cudaFree(ctx->dev_acc);
@@ -65,7 +56,7 @@ int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* 
     if (!ctx) return NB_ERR_INVALID;
     if (device) *device = ctx->device;
     if (sm_count) *sm_count = ctx->sm_count;
-    if (scratch_bytes) *scratch_bytes = ctx->packed_bytes + ctx->partial_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes;
+    if (scratch_bytes) *scratch_bytes = ctx->partial_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes;
     return NB_OK;
 }
 

@@ -14,10 +14,9 @@ struct nb_context {
     int device = 0;
     int sm_count = 0;
     char err[512] = {0};
+    int max_bodies = 0;
 
     // direct path scratch
-    void* packed = nullptr;       // duplicated source records, 32 B per source (see direct.cu)
-    size_t packed_bytes = 0;
     void* partial = nullptr;      // float4[jsplit][targets] partial sums when the source range is split
     size_t partial_bytes = 0;
     void* dev_pos = nullptr;      // staging for the *_host entry points

@@ -8,48 +8,69 @@
 //     s   = ((inv*inv)*inv)*m_j   [2D: (inv*inv)*m_j]  (:66 / :28)
 //     a  += d*s  (fma)                                 (:67)
 // What is different is everything around it:
-//   * FP32x2 packed math (FADD2/FFMA2/FMUL2): one instruction serves two targets of the same thread, so the
-//     12 FP32-pipe operations of an interaction cost 6 issue slots and the FMA pipe, not the scheduler, is
-//     the limit.  The source operand of a packed op must be a register pair holding the same value twice;
-//     sources are therefore pre-packed once per evaluation into 32-byte records {x,x,y,y | z,z,m,m}.
-//   * each thread owns 2*PAIRS targets in registers; one pair of broadcast LDS.128 serves all of them.
-//   * source tiles stream into shared memory with cp.async.bulk (TMA, UBLKCP) into a 3-stage ring guarded
-//     by mbarriers; no __syncthreads in the main loop.
+//   * FP32x2 packed math (FADD2/FFMA2/FMUL2): one instruction serves two targets of the same thread; the
+//     source coordinate enters as a scalar-broadcast operand (SASS `R.F32`), so a source costs one LDS.128.
+//     Scalar FFMA with three distinct register operands is register-bank limited to ~64 % of the FP32 lane
+//     peak on B200 (profiles/ubench), the packed form reaches 99 %.
+//   * each thread owns 2*PAIRS targets in registers; one broadcast LDS.128 per source serves all of them.
+//   * source tiles stream from `pos` into shared memory with cp.async.bulk (TMA, UBLKCP) into a 3-stage ring
+//     guarded by mbarriers; no __syncthreads in the main loop and no staging copy of the sources.
 //   * the source range can be split over blockIdx.y (partials reduced in fixed order -> deterministic) so
 //     that small target counts (N = 16,384; an 1/8 slice of 1M on 8 GPUs) still fill 148 SMs.
+// Measured dispatch model (profiles/README.md): an SM sub-partition spends 2 cycles per packed FP32x2
+// instruction, ~2 per MUFU and 1 per anything else, so the loop is kept free of everything else.
 #include "common.cuh"
 
 namespace {
 
 constexpr int NT = 256;      // threads per CTA
-constexpr int TILE = 512;    // sources per pipeline stage (16 KB)
+constexpr int TILE = 1024;   // sources per pipeline stage (16 KB)
 constexpr int STAGES = 3;
-constexpr int REC_BYTES = 32;
+constexpr int REC_BYTES = 16;
 constexpr int SMEM_BYTES = STAGES * TILE * REC_BYTES + 2 * STAGES * 8;
 
-__global__ void pack_sources_kernel(const float4* __restrict__ pos, int n, int n_pad, float4* __restrict__ packed) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_pad) return;
-    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);  // padding: massless body at the origin adds exactly 0
-    if (i < n) p = pos[i];
-    packed[2 * (size_t)i] = make_float4(p.x, p.x, p.y, p.y);
-    packed[2 * (size_t)i + 1] = make_float4(p.z, p.z, p.w, p.w);
+template <int DIM, int PAIRS>
+__device__ __forceinline__ void interact(const float4 s, const uint64_t (&BX)[PAIRS], const uint64_t (&BY)[PAIRS],
+                                         const uint64_t (&BZ)[PAIRS], uint64_t (&AX)[PAIRS], uint64_t (&AY)[PAIRS],
+                                         uint64_t (&AZ)[PAIRS], const uint64_t E2) {
+    const uint64_t sx = pk2(s.x, s.x), sy = pk2(s.y, s.y), sz = pk2(s.z, s.z), sm = pk2(s.w, s.w);
+#pragma unroll
+    for (int p = 0; p < PAIRS; p++) {
+        uint64_t dx = sub2(sx, BX[p]);
+        uint64_t dy = sub2(sy, BY[p]);
+        uint64_t r2 = fma2(dx, dx, E2);
+        r2 = fma2(dy, dy, r2);
+        uint64_t dz;
+        if (DIM == 3) {
+            dz = sub2(sz, BZ[p]);
+            r2 = fma2(dz, dz, r2);
+        }
+        float r0, r1;
+        up2(r2, r0, r1);
+        uint64_t inv = pk2(rsqrt_approx(r0), rsqrt_approx(r1));
+        uint64_t sc = mul2(inv, inv);
+        if (DIM == 3) sc = mul2(sc, inv);
+        sc = mul2(sc, sm);
+        AX[p] = fma2(dx, sc, AX[p]);
+        AY[p] = fma2(dy, sc, AY[p]);
+        if (DIM == 3) AZ[p] = fma2(dz, sc, AZ[p]);
+    }
 }
 
 template <int DIM, int PAIRS, int MINB>
 __global__ void __launch_bounds__(NT, MINB)
-direct_kernel(const float4* __restrict__ pos,     // all bodies (targets are read from here)
-              const float4* __restrict__ packed,  // duplicated sources, ntiles*TILE records
-              int ntiles, int target_begin, int target_count, float eps,
+direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and targets are read from here too
+              int n, int target_begin, int target_count, float eps,
               float4* __restrict__ out,           // acc (jsplit == 1) or partial sums [jsplit][target_count]
               int jsplit) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const ulonglong2* tiles = reinterpret_cast<const ulonglong2*>(smem);
+    const float4* tiles = reinterpret_cast<const float4*>(smem);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * TILE * REC_BYTES);
     uint64_t* empty = full + STAGES;
 
     const int tid = threadIdx.x;
     const int js = blockIdx.y;
+    const int ntiles = (n + TILE - 1) / TILE;
     const int tile0 = (int)((long long)ntiles * js / jsplit);
     const int tile1 = (int)((long long)ntiles * (js + 1) / jsplit);
     const int my_tiles = tile1 - tile0;
@@ -71,6 +92,13 @@ direct_kernel(const float4* __restrict__ pos,     // all bodies (targets are rea
     }
     const uint64_t E2 = pk2(eps, eps);
 
+    auto tile_count = [&](int t) { return min(TILE, n - t * TILE); };  // bodies in global tile t
+    auto issue = [&](int t, int s) {                                  // one thread: TMA tile t -> stage s
+        const uint32_t bytes = (uint32_t)tile_count(t) * REC_BYTES;
+        mbar_expect_tx(&full[s], bytes);
+        bulk_g2s(smem + s * TILE * REC_BYTES, pos + (size_t)t * TILE, bytes, &full[s]);
+    };
+
     if (tid == 0) {
         for (int s = 0; s < STAGES; s++) {
             mbar_init(&full[s], 1);
@@ -81,41 +109,19 @@ direct_kernel(const float4* __restrict__ pos,     // all bodies (targets are rea
     __syncthreads();
     if (tid == 0) {
         const int pre = my_tiles < STAGES ? my_tiles : STAGES;
-        for (int s = 0; s < pre; s++) {
-            mbar_expect_tx(&full[s], TILE * REC_BYTES);
-            bulk_g2s(smem + s * TILE * REC_BYTES, packed + 2 * (size_t)(tile0 + s) * TILE, TILE * REC_BYTES, &full[s]);
-        }
+        for (int s = 0; s < pre; s++) issue(tile0 + s, s);
     }
 
     for (int it = 0; it < my_tiles; it++) {
         const int s = it % STAGES;
         mbar_wait(&full[s], (it / STAGES) & 1);
-        const ulonglong2* tp = tiles + s * (TILE * 2);
-#pragma unroll 2
-        for (int j = 0; j < TILE; j++) {
-            const ulonglong2 a = tp[2 * j];      // (x,x) (y,y)
-            const ulonglong2 b = tp[2 * j + 1];  // (z,z) (m,m)
-#pragma unroll
-            for (int p = 0; p < PAIRS; p++) {
-                uint64_t dx = sub2(a.x, BX[p]);
-                uint64_t dy = sub2(a.y, BY[p]);
-                uint64_t r2 = fma2(dx, dx, E2);
-                r2 = fma2(dy, dy, r2);
-                uint64_t dz;
-                if (DIM == 3) {
-                    dz = sub2(b.x, BZ[p]);
-                    r2 = fma2(dz, dz, r2);
-                }
-                float r0, r1;
-                up2(r2, r0, r1);
-                uint64_t inv = pk2(rsqrt_approx(r0), rsqrt_approx(r1));
-                uint64_t sc = mul2(inv, inv);
-                if (DIM == 3) sc = mul2(sc, inv);
-                sc = mul2(sc, b.y);
-                AX[p] = fma2(dx, sc, AX[p]);
-                AY[p] = fma2(dy, sc, AY[p]);
-                if (DIM == 3) AZ[p] = fma2(dz, sc, AZ[p]);
-            }
+        const float4* tp = tiles + s * TILE;
+        const int cnt = tile_count(tile0 + it);
+        if (cnt == TILE) {
+#pragma unroll 4
+            for (int j = 0; j < TILE; j++) interact<DIM, PAIRS>(tp[j], BX, BY, BZ, AX, AY, AZ, E2);
+        } else {  // ragged last tile of the source array
+            for (int j = 0; j < cnt; j++) interact<DIM, PAIRS>(tp[j], BX, BY, BZ, AX, AY, AZ, E2);
         }
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
@@ -126,9 +132,7 @@ direct_kernel(const float4* __restrict__ pos,     // all bodies (targets are rea
             if (nxt < my_tiles) {
                 const int sp = prev % STAGES;
                 mbar_wait(&empty[sp], (prev / STAGES) & 1);
-                mbar_expect_tx(&full[sp], TILE * REC_BYTES);
-                bulk_g2s(smem + sp * TILE * REC_BYTES, packed + 2 * (size_t)(tile0 + nxt) * TILE, TILE * REC_BYTES,
-                         &full[sp]);
+                issue(tile0 + nxt, sp);
             }
         }
     }
@@ -168,7 +172,7 @@ __global__ void zero_acc_kernel(float4* acc, int n) {
     if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-using kernel_fn = void (*)(const float4*, const float4*, int, int, int, float, float4*, int);
+using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int);
 
 struct Variant {
     kernel_fn fn;
@@ -199,9 +203,7 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
 
     const int ntiles = (n + TILE - 1) / TILE;
-    const int n_pad = ntiles * TILE;
-    int rc = nb_reserve(ctx, &ctx->packed, &ctx->packed_bytes, (size_t)n_pad * REC_BYTES);
-    if (rc) return rc;
+    int rc = NB_OK;
 
     // choose the register blocking: 8 targets/thread when there are enough targets to fill the GPU with
     // them, else 4 (finer granularity); NB_DIRECT_PAIRS overrides for tuning.
@@ -225,7 +227,7 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
         if (forced > 0) {
             jsplit = forced < ntiles ? forced : ntiles;
         } else {
-            int max_js = ntiles / 4;  // keep >= 4 tiles (2048 sources) per CTA
+            int max_js = ntiles / 2;  // keep >= 2 tiles (2048 sources) per CTA
             if (max_js > 64) max_js = 64;
             if (max_js < 1) max_js = 1;
             double best = -1.0;
@@ -250,17 +252,14 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
         out = reinterpret_cast<float4*>(ctx->partial);
     }
 
-    pack_sources_kernel<<<(n_pad + 255) / 256, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, n_pad,
-                                                                 reinterpret_cast<float4*>(ctx->packed));
     dim3 grid(tblocks, jsplit);
-    v.fn<<<grid, NT, SMEM_BYTES, stream>>>(reinterpret_cast<const float4*>(pos),
-                                           reinterpret_cast<const float4*>(ctx->packed), ntiles, target_begin,
-                                           target_count, softening, out, jsplit);
-    int launches = 2;
+    v.fn<<<grid, NT, SMEM_BYTES, stream>>>(reinterpret_cast<const float4*>(pos), n, target_begin, target_count,
+                                           softening, out, jsplit);
+    int launches = 1;
     if (jsplit > 1) {
         reduce_partials_kernel<<<(target_count + 255) / 256, 256, 0, stream>>>(
             reinterpret_cast<const float4*>(ctx->partial), target_count, jsplit, reinterpret_cast<float4*>(acc));
-        launches = 3;
+        launches = 2;
     }
     NB_CUDA(ctx, cudaGetLastError());
     ctx->last_jsplit = jsplit;
