@@ -52,6 +52,9 @@ extern "C" {
 #define NB_BH_ACCUMULATE_BOUNDS 1  /* reference behaviour: d_bounds is the running union over all calls,
                                       src/BarnesHutKernels.cu:190-193 + src/ComputeMethods.cpp:40 */
 
+#define NB_BH_COUNT_WALK 0x100      /* instrumented walk: also fills the counters of nb_bh_last_counters
+                                      (nodes opened, children examined, ...); slower, for roofline accounting */
+
 typedef struct nb_context nb_context;
 
 /* ---- lifetime ------------------------------------------------------------------------------------ */

@@ -17,7 +17,7 @@ _lib = None
 
 NB_OK = 0
 NB_DIRECT_AUTO, NB_DIRECT_ORDERED = 0, 1
-NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS = 0, 1
+NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS, NB_BH_COUNT_WALK = 0, 1, 0x100
 
 # every symbol include/nbody_b200.h declares (tests check that the library exports each one)
 ABI_SYMBOLS = [

@@ -1,25 +1,988 @@
-// bh.cu -- Barnes-Hut pipeline (placeholder until the stages land).
+// bh.cu -- Barnes-Hut force pipeline for sm_100a (2D quadtree, like the reference).
+//
+// Replaces barnesHutCompute and its kernels (reference src/BarnesHutKernels.cu:11-70,108-451) with one
+// stream-ordered pipeline (no host synchronisation, no per-call allocation):
+//
+//   bounds  -> keys -> sort(SFC) , sort(tree) -> gather + FP64 prefix sums -> boundaries -> node ids -> emit -> walk
+//
+// Parity contract (BASELINE.json north_star):
+//   * bounds, SFC keys and the sort permutation are bit-exact against the reference (float bisection with
+//     the same comparisons, fmaf padding, stable LSD radix sort);
+//   * the tree has the reference's topology -- the bucket-1 region quadtree over the padded box obtained
+//     by '>=' bisection (src/BarnesHutKernels.cu:266-293) -- but it is built WITHOUT locks, atomics or
+//     insertion order: bodies are sorted by their 64-bit tree-path key and every internal node is found
+//     from the sorted keys alone (common-prefix searches), so node ids and monopoles are deterministic.
+//     Chains of single-child cells are stored once (compressed) with the level at which they finally split;
+//     nb_bh_export_tree expands them again for the canonical comparison;
+//   * centres of mass come from FP64 prefix sums over the sorted bodies (no float atomicAdd);
+//   * the walk keeps the reference's acceptance rule: groups of 32 consecutive entries of the SFC
+//     permutation vote unanimously, a cell is tested against its parent's width, level-1 cells are always
+//     opened, bodies are always summed (src/BarnesHutKernels.cu:398-445), same LIFO order, same FP32
+//     arithmetic per interaction.
 #include "common.cuh"
 
-void nb_bh_destroy(nb_context* ctx) { (void)ctx; }
+#include <algorithm>
+#include <cfloat>
+#include <vector>
+
+namespace {
+
+constexpr int MAX_LEVEL = 32;             // depth cap: 32 levels of bisection = 64-bit keys; deeper cells become buckets
+constexpr uint32_t LINK_EMPTY = 0xFFFFFFFFu;
+constexpr uint32_t LINK_BODY = 0xFFFFFFFEu;
+constexpr uint32_t KIND_BUCKET = 63u;     // link = (level << 26) | node id ; level field 63 marks a bucket node
+constexpr int WALK_STACK = 128;           // >= 3 * 33 + 1
+
+struct D3 {
+    double m, mx, my;
+};
+__host__ __device__ inline D3 operator+(const D3& a, const D3& b) { return D3{a.m + b.m, a.mx + b.mx, a.my + b.my}; }
+
+}  // namespace
+
+struct nb_bh_state {
+    int cap = 0;           // bodies the buffers are sized for
+    bool bounds_valid = false;
+    float4* bounds = nullptr;          // (minX, minY, maxX, maxY)
+    float4* bounds_part = nullptr;     // per-block partials
+    unsigned int* ticket = nullptr;
+    uint32_t* key32[2] = {nullptr, nullptr};
+    int32_t* idx32[2] = {nullptr, nullptr};
+    uint64_t* key64[2] = {nullptr, nullptr};
+    int32_t* idx64[2] = {nullptr, nullptr};
+    uint32_t* hist = nullptr;          // radix histograms [256][blocks]
+    size_t hist_elems = 0;
+    float4* spos = nullptr;            // bodies in tree order: (x, y, m, -)
+    D3* psum = nullptr;                // chunk-local inclusive prefix sums of (m, m x, m y)
+    D3* psum_blk = nullptr;            // exclusive prefix of the chunk totals
+    int32_t* left = nullptr;           // per boundary: left extent of its node
+    int32_t* flag_scan = nullptr;      // chunk-local inclusive scan of leader flags
+    int32_t* flag_blk = nullptr;
+    float4* cblk = nullptr;            // child blocks, 4 x float4 per node
+    int32_t* node_first = nullptr;
+    int32_t* node_last = nullptr;
+    int8_t* node_level = nullptr;
+    int8_t* node_top = nullptr;        // first level of the chain this node compresses
+    int32_t* root = nullptr;           // [0] root node id
+    float4* root_rec = nullptr;        // the root cell as a child record (cx, cy, m, link)
+    unsigned long long* counters = nullptr;  // opened, examined, interactions, max stack, overflow flag
+    int last_n = 0;
+    // result locations of the last sorts
+    int sfc_sel = 0, tree_sel = 0;
+};
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------------
+// bounds: global min/max of x and y, padded by 0.1 % of |coord|   (src/BarnesHutKernels.cu:152-195)
+// ------------------------------------------------------------------------------------------------------
+__global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* part,
+                              unsigned int* __restrict__ ticket, float4* __restrict__ bounds, int accumulate) {
+    float mnx = FLT_MAX, mny = FLT_MAX, mxx = -FLT_MAX, mxy = -FLT_MAX;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 p = pos[i];
+        mnx = fminf(mnx, p.x);
+        mny = fminf(mny, p.y);
+        mxx = fmaxf(mxx, p.x);
+        mxy = fmaxf(mxy, p.y);
+    }
+    __shared__ float4 sh[32];
+    __shared__ bool last;
+    auto warp_red = [&]() {
+        for (int o = 16; o > 0; o >>= 1) {
+            mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
+            mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+            mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+            mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+        }
+    };
+    auto block_red = [&]() {
+        warp_red();
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = make_float4(mnx, mny, mxx, mxy);
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            float4 v = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : make_float4(FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX);
+            mnx = v.x; mny = v.y; mxx = v.z; mxy = v.w;
+            warp_red();
+        }
+        __syncthreads();
+    };
+    block_red();
+    if (threadIdx.x == 0) {
+        part[blockIdx.x] = make_float4(mnx, mny, mxx, mxy);
+        __threadfence();
+        last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    mnx = FLT_MAX; mny = FLT_MAX; mxx = -FLT_MAX; mxy = -FLT_MAX;
+    for (int b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+        const float4 v = __ldcg(&part[b]);   // written by other blocks of this launch: read through L2
+        mnx = fminf(mnx, v.x); mny = fminf(mny, v.y); mxx = fmaxf(mxx, v.z); mxy = fmaxf(mxy, v.w);
+    }
+    block_red();
+    if (threadIdx.x == 0) {
+        // pad: the reference's `v - fabsf(v) * 0.001f` is one FFMA on sm_100
+        float b0 = __fmaf_rn(fabsf(mnx), -0.001f, mnx);
+        float b1 = __fmaf_rn(fabsf(mny), -0.001f, mny);
+        float b2 = __fmaf_rn(fabsf(mxx), 0.001f, mxx);
+        float b3 = __fmaf_rn(fabsf(mxy), 0.001f, mxy);
+        if (accumulate) {  // reference behaviour: running union with the previous box
+            const float4 o = *bounds;
+            b0 = fminf(b0, o.x); b1 = fminf(b1, o.y); b2 = fmaxf(b2, o.z); b3 = fmaxf(b3, o.w);
+        }
+        *bounds = make_float4(b0, b1, b2, b3);
+        *ticket = 0u;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// keys: SFC key (src/BarnesHutKernels.cu:197-240, strict '>') and 64-bit tree-path key (the '>=' descent of
+// :266-285, digit = path ^ 2 so that both orders agree away from exact midpoint hits)
+// ------------------------------------------------------------------------------------------------------
+__global__ void keys_kernel(const float4* __restrict__ pos, int n, const float4* __restrict__ bounds,
+                            uint32_t* __restrict__ key32, int32_t* __restrict__ idx32,
+                            uint64_t* __restrict__ key64, int32_t* __restrict__ idx64) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 bb = *bounds;
+    const float4 p = pos[i];
+    {
+        float l = bb.x, r = bb.z, b = bb.y, t = bb.w;
+        uint32_t key = 0;
+#pragma unroll
+        for (int s = 30; s >= 0; s -= 2) {
+            const float midX = (r + l) * 0.5f;
+            const float midY = (t + b) * 0.5f;
+            if (p.x > midX) {
+                l = midX;
+                if (p.y > midY) { b = midY; key |= 1u << s; }
+                else            { t = midY; key |= 3u << s; }
+            } else {
+                r = midX;
+                if (p.y > midY) { b = midY; }
+                else            { t = midY; key |= 2u << s; }
+            }
+        }
+        key32[i] = key;
+        idx32[i] = i;
+    }
+    {
+        float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
+        uint64_t key = 0;
+#pragma unroll 8
+        for (int lev = 0; lev < MAX_LEVEL; lev++) {
+            unsigned path = 0;
+            const float midX = (maxX + minX) * 0.5f;
+            if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
+            const float midY = (maxY + minY) * 0.5f;
+            if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
+            key |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
+        }
+        key64[i] = key;
+        idx64[i] = i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// stable LSD radix sort, 8-bit digits (replaces thrust::sort_by_key, src/BarnesHutKernels.cu:45)
+// ------------------------------------------------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 keys per block
+
+template <typename K>
+__global__ void __launch_bounds__(SORT_THREADS) sort_hist_kernel(const K* __restrict__ keys, int n, int shift,
+                                                                uint32_t* __restrict__ hist, int nblocks) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * SORT_TILE;
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int i = base + k * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(uint32_t)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];  // digit-major
+}
+
+// exclusive scan of `count` uint32 in place, one block (count = 256 * nblocks)
+__global__ void __launch_bounds__(1024) scan_u32_kernel(uint32_t* __restrict__ data, int count) {
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int per = 8;
+    for (int base = 0; base < count; base += 1024 * per) {
+        uint32_t v[per];
+        uint32_t s = 0;
+        const int i0 = base + threadIdx.x * per;
+#pragma unroll
+        for (int k = 0; k < per; k++) {
+            v[k] = (i0 + k < count) ? data[i0 + k] : 0u;
+            s += v[k];
+        }
+        uint32_t inc = s;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if ((threadIdx.x & 31) >= o) inc += t;
+        }
+        if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = wsum[threadIdx.x];
+            uint32_t winc = w;
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+                if (threadIdx.x >= o) winc += t;
+            }
+            wsum[threadIdx.x] = winc - w;  // exclusive over warps
+        }
+        __syncthreads();
+        uint32_t run = carry_s + wsum[threadIdx.x >> 5] + (inc - s);
+#pragma unroll
+        for (int k = 0; k < per; k++) {
+            if (i0 + k < count) data[i0 + k] = run;
+            run += v[k];
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = run;
+        __syncthreads();
+    }
+}
+
+template <typename K>
+__global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __restrict__ keys_in,
+                                                                   const int32_t* __restrict__ vals_in, int n, int shift,
+                                                                   const uint32_t* __restrict__ offs, int nblocks,
+                                                                   K* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
+    // tile order = warp-major, round-major, lane: warp w owns keys [w*512, (w+1)*512) of the tile
+    constexpr int WARPS = SORT_THREADS / 32;
+    __shared__ uint32_t cnt[WARPS][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int d = lane; d < 256; d += 32) cnt[warp][d] = 0;
+    __syncwarp();
+    const int wbase = blockIdx.x * SORT_TILE + warp * (32 * SORT_ITEMS);
+    K key[SORT_ITEMS];
+    uint32_t rank[SORT_ITEMS];
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int i = wbase + k * 32 + lane;
+        const bool valid = i < n;
+        key[k] = valid ? keys_in[i] : (K)0;
+        rank[k] = 0;
+        const unsigned act = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
+            const unsigned peers = __match_any_sync(act, d);
+            const int leader = __ffs(peers) - 1;
+            uint32_t basev = 0;
+            if (lane == leader) {
+                basev = cnt[warp][d];
+                cnt[warp][d] = basev + __popc(peers);
+            }
+            basev = __shfl_sync(peers, basev, leader);
+            rank[k] = basev + __popc(peers & ((1u << lane) - 1u));
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // per digit: exclusive prefix over warps, plus the global offset of this block's digit bin
+        const int d = threadIdx.x;
+        uint32_t run = offs[(size_t)d * nblocks + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) {
+            const uint32_t c = cnt[w][d];
+            cnt[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int i = wbase + k * 32 + lane;
+        if (i < n) {
+            const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
+            const uint32_t dst = cnt[warp][d] + rank[k];
+            keys_out[dst] = key[k];
+            vals_out[dst] = vals_in[i];
+        }
+    }
+}
+
+template <typename K>
+int radix_sort(nb_context* ctx, nb_bh_state* st, K* keys[2], int32_t* vals[2], int n, int bits, int* sel_out,
+               cudaStream_t stream) {
+    const int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+    int sel = 0;
+    for (int shift = 0; shift < bits; shift += 8) {
+        sort_hist_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], n, shift, st->hist, nblocks);
+        scan_u32_kernel<<<1, 1024, 0, stream>>>(st->hist, 256 * nblocks);
+        sort_scatter_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], vals[sel], n, shift, st->hist, nblocks,
+                                                                    keys[sel ^ 1], vals[sel ^ 1]);
+        sel ^= 1;
+    }
+    *sel_out = sel;
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// chunked scans (chunk = 2048 elements per block): local inclusive prefix + exclusive prefix of chunk totals
+// ------------------------------------------------------------------------------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_CHUNK = SCAN_THREADS * SCAN_ITEMS;  // 2048
+constexpr int SCAN_SHIFT = 11;
+
+template <typename T>
+__device__ __forceinline__ T shfl_up_t(T v, int o);
+template <>
+__device__ __forceinline__ int shfl_up_t<int>(int v, int o) { return __shfl_up_sync(0xffffffffu, v, o); }
+template <>
+__device__ __forceinline__ D3 shfl_up_t<D3>(D3 v, int o) {
+    return D3{__shfl_up_sync(0xffffffffu, v.m, o), __shfl_up_sync(0xffffffffu, v.mx, o), __shfl_up_sync(0xffffffffu, v.my, o)};
+}
+__device__ __forceinline__ int zero_of(int) { return 0; }
+__device__ __forceinline__ D3 zero_of(D3) { return D3{0.0, 0.0, 0.0}; }
+
+// v[] holds the thread's SCAN_ITEMS consecutive inputs; on return they hold the chunk-local inclusive scan.
+template <typename T>
+__device__ __forceinline__ void block_scan_chunk(T (&v)[SCAN_ITEMS], T* total_out) {
+    __shared__ T wtot[SCAN_THREADS / 32];
+    T s = v[0];
+#pragma unroll
+    for (int k = 1; k < SCAN_ITEMS; k++) { s = s + v[k]; v[k] = s; }
+    T inc = s;
+    for (int o = 1; o < 32; o <<= 1) {
+        T t = shfl_up_t<T>(inc, o);
+        if ((threadIdx.x & 31) >= o) inc = t + inc;
+    }
+    if ((threadIdx.x & 31) == 31) wtot[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    T off = zero_of(T());
+    const int w = threadIdx.x >> 5;
+    for (int k = 0; k < w; k++) off = off + wtot[k];
+    T excl = shfl_up_t<T>(inc, 1);
+    if ((threadIdx.x & 31) == 0) excl = zero_of(T());
+    off = off + excl;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) v[k] = off + v[k];
+    if (threadIdx.x == SCAN_THREADS - 1 && total_out) *total_out = v[SCAN_ITEMS - 1];
+}
+
+// one block: exclusive scan of the chunk totals in place
+template <typename T>
+__global__ void __launch_bounds__(1024) scan_totals_kernel(T* __restrict__ tot, int count) {
+    __shared__ T wtot[32];
+    __shared__ T carry_s;
+    if (threadIdx.x == 0) carry_s = zero_of(T());
+    __syncthreads();
+    for (int base = 0; base < count; base += 1024) {
+        const int i = base + threadIdx.x;
+        const T v = i < count ? tot[i] : zero_of(T());
+        T inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            T t = shfl_up_t<T>(inc, o);
+            if ((threadIdx.x & 31) >= o) inc = t + inc;
+        }
+        if ((threadIdx.x & 31) == 31) wtot[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        T off = carry_s;
+        for (int k = 0; k < (int)(threadIdx.x >> 5); k++) off = off + wtot[k];
+        T excl = shfl_up_t<T>(inc, 1);
+        if ((threadIdx.x & 31) == 0) excl = zero_of(T());
+        const T mine = off + excl;  // exclusive
+        if (i < count) tot[i] = mine;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = mine + v;
+        __syncthreads();
+    }
+}
+
+// gather bodies into tree order and scan (m, m*x, m*y) in FP64
+__global__ void __launch_bounds__(SCAN_THREADS) gather_scan_kernel(const float4* __restrict__ pos,
+                                                                  const int32_t* __restrict__ order, int n,
+                                                                  float4* __restrict__ spos, D3* __restrict__ psum,
+                                                                  D3* __restrict__ tot) {
+    D3 v[SCAN_ITEMS];
+    const int i0 = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const int i = i0 + k;
+        if (i < n) {
+            const float4 p = pos[order[i]];
+            spos[i] = make_float4(p.x, p.y, p.w, 0.f);
+            v[k] = D3{(double)p.w, (double)p.w * (double)p.x, (double)p.w * (double)p.y};
+        } else {
+            v[k] = D3{0.0, 0.0, 0.0};
+        }
+    }
+    block_scan_chunk<D3>(v, &tot[blockIdx.x]);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++)
+        if (i0 + k < n) psum[i0 + k] = v[k];
+}
+
+// ------------------------------------------------------------------------------------------------------
+// tree from sorted keys
+// ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int cpl(uint64_t a, uint64_t b) {  // common prefix, in levels
+    const uint64_t x = a ^ b;
+    return x ? (__clzll((long long)x) >> 1) : MAX_LEVEL;
+}
+
+// smallest a in [0, i] with cpl(K[a], K[i]) >= L
+__device__ __forceinline__ int left_extent(const uint64_t* __restrict__ K, int i, int L) {
+    const uint64_t ki = K[i];
+    int good = i, step = 1;
+    while (good - step >= 0 && cpl(K[good - step], ki) >= L) { good -= step; step <<= 1; }
+    int bad = good - step;
+    if (bad < -1) bad = -1;
+    while (good - bad > 1) {
+        const int mid = (good + bad) >> 1;
+        if (cpl(K[mid], ki) >= L) good = mid; else bad = mid;
+    }
+    return good;
+}
+// largest b in [i, limit] with cpl(K[i], K[b]) >= L
+__device__ __forceinline__ int right_extent(const uint64_t* __restrict__ K, int i, int limit, int L) {
+    const uint64_t ki = K[i];
+    int good = i, step = 1;
+    while (good + step <= limit && cpl(ki, K[good + step]) >= L) { good += step; step <<= 1; }
+    int bad = good + step;
+    if (bad > limit + 1) bad = limit + 1;
+    while (bad - good > 1) {
+        const int mid = (good + bad) >> 1;
+        if (cpl(ki, K[mid]) >= L) good = mid; else bad = mid;
+    }
+    return good;
+}
+
+// per boundary i (between sorted bodies i and i+1): is it the leftmost separator of its node?
+__global__ void __launch_bounds__(SCAN_THREADS) boundary_kernel(const uint64_t* __restrict__ K, int n,
+                                                               int32_t* __restrict__ left, int32_t* __restrict__ flag_scan,
+                                                               int32_t* __restrict__ tot) {
+    int v[SCAN_ITEMS];
+    const int i0 = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const int i = i0 + k;
+        int f = 0;
+        if (i < n - 1) {
+            const int L = cpl(K[i], K[i + 1]);
+            const int a = left_extent(K, i, L);
+            f = (a == i) || (cpl(K[a], K[i]) > L);
+            left[i] = a;
+        }
+        v[k] = f;
+    }
+    block_scan_chunk<int>(v, &tot[blockIdx.x]);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++)
+        if (i0 + k < n - 1) flag_scan[i0 + k] = v[k];
+}
+
+struct TreeView {
+    const uint64_t* K;
+    const float4* spos;
+    const D3* psum;
+    const D3* psum_blk;
+    const int32_t* flag_scan;
+    const int32_t* flag_blk;
+    int n;
+};
+
+__device__ __forceinline__ D3 prefix_incl(const TreeView& t, int i) {  // sum over sorted bodies [0, i]
+    const D3 a = t.psum[i], b = t.psum_blk[i >> SCAN_SHIFT];
+    return D3{a.m + b.m, a.mx + b.mx, a.my + b.my};
+}
+__device__ __forceinline__ int flag_incl(const TreeView& t, int i) { return t.flag_scan[i] + t.flag_blk[i >> SCAN_SHIFT]; }
+
+__global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __restrict__ left,
+                                                  float4* __restrict__ cblk, int32_t* __restrict__ node_first,
+                                                  int32_t* __restrict__ node_last, int8_t* __restrict__ node_level,
+                                                  int8_t* __restrict__ node_top, int32_t* __restrict__ root,
+                                                  float4* __restrict__ root_rec) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= t.n - 1) return;
+    const int incl = flag_incl(t, i);
+    const int prev = i > 0 ? flag_incl(t, i - 1) : 0;
+    if (incl == prev) return;          // not a leader
+    const int id = prev;               // exclusive scan = node id
+    const uint64_t* K = t.K;
+    const int L = cpl(K[i], K[i + 1]);
+    const int a = left[i];
+    const int b = right_extent(K, i + 1, t.n - 1, L);
+    node_first[id] = a;
+    node_last[id] = b;
+    node_level[id] = (int8_t)L;
+    if (a == 0 && b == t.n - 1) {
+        root[0] = id;
+        node_top[id] = 0;
+        const D3 all = prefix_incl(t, t.n - 1);
+        float cx = 0.f, cy = 0.f;
+        if (all.m > 0.0) { cx = (float)(all.mx / all.m); cy = (float)(all.my / all.m); }
+        const uint32_t lev = L >= MAX_LEVEL ? KIND_BUCKET : (uint32_t)L;
+        *root_rec = make_float4(cx, cy, (float)all.m, __uint_as_float((lev << 26) | (uint32_t)id));
+    }
+    float4* blk = cblk + 4 * (size_t)id;
+    if (L >= MAX_LEVEL) {  // bucket: all keys equal; the walk sums bodies [a, b] directly
+        blk[0] = make_float4(__int_as_float(a), __int_as_float(b - a + 1), 0.f, 0.f);
+        return;
+    }
+    float4 rec[4];
+#pragma unroll
+    for (int s = 0; s < 4; s++) rec[s] = make_float4(0.f, 0.f, 0.f, __uint_as_float(LINK_EMPTY));
+    int c0 = a;
+    while (c0 <= b) {
+        const int e = right_extent(K, c0, b, L + 1);
+        const int slot = (int)((K[c0] >> (62 - 2 * L)) & 3ull) ^ 2;   // path = digit ^ 2
+        float4 r;
+        if (e == c0) {
+            const float4 p = t.spos[c0];
+            r = make_float4(p.x, p.y, p.z, __uint_as_float(LINK_BODY));
+        } else {
+            const D3 hi = prefix_incl(t, e);
+            D3 lo = D3{0.0, 0.0, 0.0};
+            if (c0 > 0) lo = prefix_incl(t, c0 - 1);
+            const double m = hi.m - lo.m;
+            float cx = 0.f, cy = 0.f;   // centre_of_mass (src/BarnesHutKernels.cu:367-379): only where mass > 0
+            if (m > 0.0) { cx = (float)((hi.mx - lo.mx) / m); cy = (float)((hi.my - lo.my) / m); }
+            const int Lc = cpl(K[c0], K[e]);
+            const int e1 = right_extent(K, c0, e, Lc + 1);            // end of the child's first child = its leader boundary
+            const int cid = flag_incl(t, e1) - 1;
+            node_top[cid] = (int8_t)(L + 1);
+            const uint32_t lev = Lc >= MAX_LEVEL ? KIND_BUCKET : (uint32_t)Lc;
+            r = make_float4(cx, cy, (float)m, __uint_as_float((lev << 26) | (uint32_t)cid));
+        }
+#pragma unroll
+        for (int s = 0; s < 4; s++) if (s == slot) rec[s] = r;
+        c0 = e + 1;
+    }
+#pragma unroll
+    for (int s = 0; s < 4; s++) blk[s] = rec[s];
+}
+
+// ------------------------------------------------------------------------------------------------------
+// walk  (src/BarnesHutKernels.cu:381-451)
+// ------------------------------------------------------------------------------------------------------
+constexpr int WALK_WARPS = 8;
+
+template <bool COUNT>
+__global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __restrict__ pos,
+                                                              const int32_t* __restrict__ sorted_idx, int n,
+                                                              const float4* __restrict__ cblk, const float4* __restrict__ spos,
+                                                              const float4* __restrict__ root_rec,
+                                                              const float4* __restrict__ bounds, float theta, float eps,
+                                                              int group_begin, int group_count, float4* __restrict__ acc,
+                                                              unsigned long long* __restrict__ counters) {
+    __shared__ uint32_t stack_s[WALK_WARPS][WALK_STACK];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * WALK_WARPS + warp;
+    if (g >= group_count) return;
+    const int bi = (group_begin + g) * 32 + lane;
+    const bool valid = bi < n;
+    const unsigned act = __ballot_sync(0xffffffffu, valid);
+    if (!valid) return;
+    const int body = sorted_idx[bi];
+    const float4 me = pos[body];
+    const float x = me.x, y = me.y;
+    float ax = 0.f, ay = 0.f;
+    uint32_t* stack = stack_s[warp];
+
+    const float4 bb = *bounds;
+    const float dim_size = fmaxf(bb.z - bb.x, bb.w - bb.y);       // :384
+    float s0 = dim_size / theta;                                   // :403
+    s0 *= s0;                                                      // :404
+    unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
+    int c_depth = 0;
+    const int leader = __ffs(act) - 1;
+
+    auto interact = [&](float cx, float cy, float m) {
+        const float dx = cx - x, dy = cy - y;
+        const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+        const float k = rsqrt_approx(r * r) * m;                   // :431
+        ax = __fmaf_rn(k, dx, ax);
+        ay = __fmaf_rn(k, dy, ay);
+    };
+    // size^2 threshold a cell that splits at level L is tested with: s0 * 0.25^(L-1)  (:411, exact scaling)
+    auto size_of = [&](int L) { return s0 * __int_as_float((127 - 2 * (L - 1)) << 23); };
+
+    // One candidate cell or body: sum it (body, or cell accepted by every target of the group) or push it.
+    auto consider = [&](const float4 c, int& wr) {
+        const uint32_t link = __float_as_uint(c.w);
+        if (link == LINK_EMPTY) return;
+        if (COUNT) c_exam++;
+        if (link == LINK_BODY) {                                   // child < n: always summed (:430)
+            interact(c.x, c.y, c.z);
+            if (COUNT) c_inter++;
+            return;
+        }
+        const uint32_t clev = link >> 26;
+        const int Lc = clev == KIND_BUCKET ? MAX_LEVEL : (int)clev;
+        const float dx = c.x - x, dy = c.y - y;
+        const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+        bool accept = false;
+        if (Lc >= 2) accept = __all_sync(act, size_of(Lc) <= r);   // :430; level-1 cells are never tested (:398-407)
+        if (accept) {
+            const float k = rsqrt_approx(r * r) * c.z;
+            ax = __fmaf_rn(k, dx, ax);
+            ay = __fmaf_rn(k, dy, ay);
+            if (COUNT) c_inter++;
+        } else {
+            if (lane == leader) stack[wr] = link;
+            wr++;
+        }
+    };
+
+    int top;
+    {
+        int wr = 0;
+        consider(*root_rec, wr);
+        top = wr - 1;
+    }
+    __syncwarp(act);
+    while (top >= 0) {
+        if (COUNT) { c_depth = max(c_depth, top + 1); }
+        const uint32_t ent = stack[top];
+        __syncwarp(act);
+        const uint32_t id = ent & 0x03FFFFFFu;
+        const uint32_t lev = ent >> 26;
+        const float4* blk = cblk + 4 * (size_t)id;
+        if (COUNT) c_open++;
+        if (lev == KIND_BUCKET) {
+            const float4 h = blk[0];
+            const int first = __float_as_int(h.x), cnt = __float_as_int(h.y);
+            for (int k = 0; k < cnt; k++) {
+                const float4 p = spos[first + k];
+                interact(p.x, p.y, p.z);
+            }
+            if (COUNT) { c_exam += cnt; c_inter += cnt; }
+            top--;
+            continue;
+        }
+        const float4 r0 = blk[0], r1 = blk[1], r2 = blk[2], r3 = blk[3];
+        int wr = top;  // the first rejected child overwrites the popped slot (:436-440), LIFO order
+        consider(r0, wr);
+        consider(r1, wr);
+        consider(r2, wr);
+        consider(r3, wr);
+        __syncwarp(act);
+        top = wr - 1;
+    }
+    acc[body] = make_float4(ax, ay, 0.f, 0.f);
+    if (COUNT) {
+        if (lane == leader) {
+            atomicAdd(&counters[0], c_open);
+            atomicAdd(&counters[1], c_exam);
+            atomicMax(&counters[3], (unsigned long long)c_depth);
+        }
+        atomicAdd(&counters[2], c_inter);
+    }
+}
+
+__global__ void zero_acc_kernel(float4* acc, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+template <typename T>
+int alloc(nb_context* ctx, T** p, size_t count) {
+    NB_CUDA(ctx, cudaMalloc((void**)p, count * sizeof(T)));
+    return NB_OK;
+}
+
+void free_state(nb_bh_state* st) {
+    if (!st) return;
+    void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
+                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->hist, st->spos, st->psum, st->psum_blk,
+                    st->left, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
+                    st->node_top, st->root, st->root_rec, st->counters};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+}
+
+int ensure_state(nb_context* ctx, int n) {
+    if (ctx->bh && ctx->bh->cap >= n) return NB_OK;
+    NB_CUDA(ctx, cudaDeviceSynchronize());
+    bool keep_bounds = false;
+    float4 old_bounds;
+    if (ctx->bh) {
+        if (ctx->bh->bounds_valid) {
+            cudaMemcpy(&old_bounds, ctx->bh->bounds, sizeof(float4), cudaMemcpyDeviceToHost);
+            keep_bounds = true;
+        }
+        free_state(ctx->bh);
+        delete ctx->bh;
+        ctx->bh = nullptr;
+    }
+    nb_bh_state* st = new nb_bh_state();
+    ctx->bh = st;
+    const size_t cap = (size_t)std::max(n, std::max(ctx->max_bodies, 1024));
+    const size_t chunks = (cap + SCAN_CHUNK - 1) / SCAN_CHUNK + 1;
+    const size_t sblocks = (cap + SORT_TILE - 1) / SORT_TILE;
+    int rc = 0;
+    rc |= alloc(ctx, &st->bounds, 1);
+    rc |= alloc(ctx, &st->bounds_part, 1024);
+    rc |= alloc(ctx, &st->ticket, 1);
+    for (int k = 0; k < 2; k++) {
+        rc |= alloc(ctx, &st->key32[k], cap);
+        rc |= alloc(ctx, &st->idx32[k], cap);
+        rc |= alloc(ctx, &st->key64[k], cap);
+        rc |= alloc(ctx, &st->idx64[k], cap);
+    }
+    st->hist_elems = 256 * sblocks;
+    rc |= alloc(ctx, &st->hist, st->hist_elems);
+    rc |= alloc(ctx, &st->spos, cap);
+    rc |= alloc(ctx, &st->psum, cap);
+    rc |= alloc(ctx, &st->psum_blk, chunks);
+    rc |= alloc(ctx, &st->left, cap);
+    rc |= alloc(ctx, &st->flag_scan, cap);
+    rc |= alloc(ctx, &st->flag_blk, chunks);
+    rc |= alloc(ctx, &st->cblk, 4 * cap);
+    rc |= alloc(ctx, &st->node_first, cap);
+    rc |= alloc(ctx, &st->node_last, cap);
+    rc |= alloc(ctx, &st->node_level, cap);
+    rc |= alloc(ctx, &st->node_top, cap);
+    rc |= alloc(ctx, &st->root, 2);
+    rc |= alloc(ctx, &st->root_rec, 1);
+    rc |= alloc(ctx, &st->counters, 8);
+    if (rc) return NB_ERR_CUDA;
+    NB_CUDA(ctx, cudaMemset(st->ticket, 0, sizeof(unsigned int)));
+    NB_CUDA(ctx, cudaMemset(st->counters, 0, 8 * sizeof(unsigned long long)));
+    if (keep_bounds) {
+        NB_CUDA(ctx, cudaMemcpy(st->bounds, &old_bounds, sizeof(float4), cudaMemcpyHostToDevice));
+        st->bounds_valid = true;
+    }
+    st->cap = (int)cap;
+    return NB_OK;
+}
+
+// stages: 1 = bounds, 2 = keys, 3 = sorts, 4 = tree
+int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, cudaStream_t stream) {
+    int rc = ensure_state(ctx, n);
+    if (rc) return rc;
+    nb_bh_state* st = ctx->bh;
+    const float4* pos = reinterpret_cast<const float4*>(pos_);
+    st->last_n = n;
+    const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
+    int bblocks = std::min(1024, std::max(1, (n + 1023) / 1024));
+    bounds_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, accumulate);
+    st->bounds_valid = true;
+    if (upto >= 2)
+        keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(pos, n, st->bounds, st->key32[0], st->idx32[0], st->key64[0],
+                                                         st->idx64[0]);
+    if (upto >= 3) {
+        rc = radix_sort<uint32_t>(ctx, st, st->key32, st->idx32, n, 32, &st->sfc_sel, stream);
+        if (rc) return rc;
+        rc = radix_sort<uint64_t>(ctx, st, st->key64, st->idx64, n, 64, &st->tree_sel, stream);
+        if (rc) return rc;
+    }
+    if (upto >= 4 && n >= 2) {
+        const int chunks = (n + SCAN_CHUNK - 1) / SCAN_CHUNK;
+        const uint64_t* K = st->key64[st->tree_sel];
+        gather_scan_kernel<<<chunks, SCAN_THREADS, 0, stream>>>(pos, st->idx64[st->tree_sel], n, st->spos, st->psum,
+                                                               st->psum_blk);
+        scan_totals_kernel<D3><<<1, 1024, 0, stream>>>(st->psum_blk, chunks);
+        const int bchunks = (n - 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
+        boundary_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->left, st->flag_scan, st->flag_blk);
+        scan_totals_kernel<int><<<1, 1024, 0, stream>>>(st->flag_blk, bchunks);
+        TreeView tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, n};
+        emit_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->left, st->cblk, st->node_first, st->node_last,
+                                                             st->node_level, st->node_top, st->root, st->root_rec);
+    }
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
+
+int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta, float eps, int group_begin,
+             int group_count, bool count, cudaStream_t stream) {
+    nb_bh_state* st = ctx->bh;
+    const float4* pos = reinterpret_cast<const float4*>(pos_);
+    float4* acc = reinterpret_cast<float4*>(acc_);
+    if (group_count <= 0) return NB_OK;
+    if (n == 1) {
+        zero_acc_kernel<<<1, 32, 0, stream>>>(acc, 1);
+        return NB_OK;
+    }
+    const int blocks = (group_count + WALK_WARPS - 1) / WALK_WARPS;
+    if (count) {
+        cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
+        walk_kernel<true><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->spos, st->root_rec,
+                                                                 st->bounds, theta, eps, group_begin,
+                                                                 group_count, acc, st->counters);
+    } else {
+        walk_kernel<false><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->spos, st->root_rec,
+                                                                  st->bounds, theta, eps, group_begin,
+                                                                  group_count, acc, st->counters);
+    }
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
+
+int check_args(nb_context* ctx, const void* pos, const void* acc, int n, float theta) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (n < 0) return nb_fail(ctx, NB_ERR_INVALID, "n must be >= 0");
+    if (n > (1 << 26) - 2) return nb_fail(ctx, NB_ERR_INVALID, "n exceeds the 26-bit node id range (67,108,862)");
+    if (n > 0 && (!pos || !acc)) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
+    if (!(theta > 0.f)) return nb_fail(ctx, NB_ERR_INVALID, "theta must be > 0");
+    return NB_OK;
+}
+
+}  // namespace
+
+void nb_bh_destroy(nb_context* ctx) {
+    if (ctx->bh) {
+        free_state(ctx->bh);
+        delete ctx->bh;
+        ctx->bh = nullptr;
+    }
+}
+
+#define NB_BH_COUNT_FLAG NB_BH_COUNT_WALK
 
 extern "C" {
-int nb_bh_accel(nb_context* ctx, const float*, float*, int, float, float, int, void*) {
-    return nb_fail(ctx, NB_ERR_INVALID, "Barnes-Hut path not built yet");
+
+int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening, int flags,
+                       int group_begin, int group_count, void* stream) {
+    int rc = check_args(ctx, pos, acc, n, theta);
+    if (rc) return rc;
+    if (n == 0) return NB_OK;
+    const int groups = (n + 31) / 32;
+    if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)
+        return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = run_build(ctx, pos, n, flags, 4, (cudaStream_t)stream);
+    if (rc) return rc;
+    return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, (flags & NB_BH_COUNT_FLAG) != 0,
+                    (cudaStream_t)stream);
 }
-int nb_bh_accel_groups(nb_context* ctx, const float*, float*, int, float, float, int, int, int, void*) {
-    return nb_fail(ctx, NB_ERR_INVALID, "Barnes-Hut path not built yet");
+
+int nb_bh_accel(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening, int flags,
+                void* stream) {
+    return nb_bh_accel_groups(ctx, pos, acc, n, theta, softening, flags, 0, (n + 31) / 32, stream);
 }
-int nb_bh_accel_host(nb_context* ctx, const float*, float*, int, float, float, int) {
-    return nb_fail(ctx, NB_ERR_INVALID, "Barnes-Hut path not built yet");
+
+int nb_bh_accel_host(nb_context* ctx, const float* host_pos, float* host_acc, int n, float theta, float softening,
+                     int flags) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (n < 0 || (n > 0 && (!host_pos || !host_acc))) return nb_fail(ctx, NB_ERR_INVALID, "bad host buffers");
+    if (n == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t bytes = (size_t)n * 16;
+    int rc = nb_reserve(ctx, &ctx->dev_pos, &ctx->dev_pos_bytes, bytes);
+    if (rc) return rc;
+    rc = nb_reserve(ctx, &ctx->dev_acc, &ctx->dev_acc_bytes, bytes);
+    if (rc) return rc;
+    cudaStream_t s = ctx->host_stream;
+    NB_CUDA(ctx, cudaMemcpyAsync(ctx->dev_pos, host_pos, bytes, cudaMemcpyHostToDevice, s));
+    rc = nb_bh_accel(ctx, (const float*)ctx->dev_pos, (float*)ctx->dev_acc, n, theta, softening, flags, s);
+    if (rc) return rc;
+    NB_CUDA(ctx, cudaMemcpyAsync(host_acc, ctx->dev_acc, bytes, cudaMemcpyDeviceToHost, s));
+    NB_CUDA(ctx, cudaStreamSynchronize(s));
+    return NB_OK;
 }
-int nb_bh_stages_host(nb_context* ctx, const float*, int, int, float*, uint32_t*, int32_t*, uint64_t*) {
-    return nb_fail(ctx, NB_ERR_INVALID, "Barnes-Hut path not built yet");
+
+int nb_bh_stages_host(nb_context* ctx, const float* pos, int n, int flags, float* bounds, uint32_t* keys,
+                      int32_t* sorted_idx, uint64_t* tree_keys) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (n <= 0 || !pos) return nb_fail(ctx, NB_ERR_INVALID, "need n > 0 and a device pointer");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = run_build(ctx, pos, n, flags, 3, 0);
+    if (rc) return rc;
+    nb_bh_state* st = ctx->bh;
+    NB_CUDA(ctx, cudaDeviceSynchronize());
+    if (bounds) NB_CUDA(ctx, cudaMemcpy(bounds, st->bounds, 16, cudaMemcpyDeviceToHost));
+    if (sorted_idx) NB_CUDA(ctx, cudaMemcpy(sorted_idx, st->idx32[st->sfc_sel], (size_t)n * 4, cudaMemcpyDeviceToHost));
+    if (keys || tree_keys) {
+        // keys in body order: rerun the key kernel into the scratch halves the sorts no longer need
+        keys_kernel<<<(n + 255) / 256, 256>>>(reinterpret_cast<const float4*>(pos), n, st->bounds, st->key32[st->sfc_sel ^ 1],
+                                              st->idx32[st->sfc_sel ^ 1], st->key64[st->tree_sel ^ 1],
+                                              st->idx64[st->tree_sel ^ 1]);
+        NB_CUDA(ctx, cudaDeviceSynchronize());
+        if (keys) NB_CUDA(ctx, cudaMemcpy(keys, st->key32[st->sfc_sel ^ 1], (size_t)n * 4, cudaMemcpyDeviceToHost));
+        if (tree_keys) NB_CUDA(ctx, cudaMemcpy(tree_keys, st->key64[st->tree_sel ^ 1], (size_t)n * 8, cudaMemcpyDeviceToHost));
+    }
+    return NB_OK;
 }
-int nb_bh_export_tree(nb_context* ctx, int*, uint64_t*, int32_t*, int32_t*, double*, double*, double*) {
-    return nb_fail(ctx, NB_ERR_INVALID, "Barnes-Hut path not built yet");
+
+int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* level, int32_t* count, double* mass,
+                      double* cx, double* cy) {
+    if (!ctx || !n_cells) return NB_ERR_INVALID;
+    nb_bh_state* st = ctx->bh;
+    if (!st || st->last_n < 1) return nb_fail(ctx, NB_ERR_INVALID, "no tree has been built on this handle");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaDeviceSynchronize());
+    const int n = st->last_n;
+    if (n < 2) { *n_cells = 0; return NB_OK; }
+    const int chunks = (n - 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
+    // node count = total number of leader flags
+    std::vector<int32_t> fblk(chunks), fs(n - 1);
+    NB_CUDA(ctx, cudaMemcpy(fblk.data(), st->flag_blk, chunks * 4, cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(fs.data(), st->flag_scan, (size_t)(n - 1) * 4, cudaMemcpyDeviceToHost));
+    const int K = fs[n - 2] + fblk[(n - 2) >> SCAN_SHIFT];
+    std::vector<int32_t> first(K), last(K);
+    std::vector<int8_t> lev(K), top(K);
+    std::vector<uint64_t> keys(n);
+    std::vector<D3> ps(n), pb((n + SCAN_CHUNK - 1) / SCAN_CHUNK);
+    NB_CUDA(ctx, cudaMemcpy(first.data(), st->node_first, (size_t)K * 4, cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(last.data(), st->node_last, (size_t)K * 4, cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(lev.data(), st->node_level, (size_t)K, cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(top.data(), st->node_top, (size_t)K, cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(keys.data(), st->key64[st->tree_sel], (size_t)n * 8, cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(ps.data(), st->psum, (size_t)n * sizeof(D3), cudaMemcpyDeviceToHost));
+    NB_CUDA(ctx, cudaMemcpy(pb.data(), st->psum_blk, pb.size() * sizeof(D3), cudaMemcpyDeviceToHost));
+    auto pre = [&](int i) { return ps[i] + pb[i >> SCAN_SHIFT]; };
+    struct Cell { uint64_t prefix; int level, count; double m, cx, cy; };
+    std::vector<Cell> cells;
+    for (int id = 0; id < K; id++) {
+        const int a = first[id], b = last[id];
+        D3 hi = pre(b), lo = a > 0 ? pre(a - 1) : D3{0, 0, 0};
+        const double m = hi.m - lo.m;
+        const double ccx = m > 0 ? (hi.mx - lo.mx) / m : 0.0, ccy = m > 0 ? (hi.my - lo.my) / m : 0.0;
+        const uint64_t path = keys[a] ^ 0xAAAAAAAAAAAAAAAAull;   // digit ^ 2 = path index
+        for (int l = top[id]; l <= lev[id]; l++) {               // expand the compressed chain
+            const uint64_t mask = l == 0 ? 0ull : (~0ull << (64 - 2 * l));
+            cells.push_back(Cell{path & mask, l, b - a + 1, m, ccx, ccy});
+        }
+    }
+    std::sort(cells.begin(), cells.end(), [](const Cell& p, const Cell& q) {
+        return p.prefix != q.prefix ? p.prefix < q.prefix : p.level < q.level;
+    });
+    const int have = *n_cells;
+    *n_cells = (int)cells.size();
+    if (prefix) {
+        if (have < (int)cells.size()) return nb_fail(ctx, NB_ERR_INVALID, "export buffers too small");
+        for (size_t k = 0; k < cells.size(); k++) {
+            prefix[k] = cells[k].prefix; level[k] = cells[k].level; count[k] = cells[k].count;
+            mass[k] = cells[k].m; cx[k] = cells[k].cx; cy[k] = cells[k].cy;
+        }
+    }
+    return NB_OK;
 }
-int nb_bh_last_counters(nb_context* ctx, int64_t*) {
-    return nb_fail(ctx, NB_ERR_INVALID, "Barnes-Hut path not built yet");
+
+int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]) {
+    if (!ctx || !counters) return NB_ERR_INVALID;
+    nb_bh_state* st = ctx->bh;
+    if (!st) return nb_fail(ctx, NB_ERR_INVALID, "no Barnes-Hut evaluation has run on this handle");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaDeviceSynchronize());
+    unsigned long long c[8];
+    NB_CUDA(ctx, cudaMemcpy(c, st->counters, sizeof(c), cudaMemcpyDeviceToHost));
+    int nodes = 0;
+    const int n = st->last_n;
+    if (n >= 2) {
+        int32_t a = 0, b = 0;
+        NB_CUDA(ctx, cudaMemcpy(&a, st->flag_scan + (n - 2), 4, cudaMemcpyDeviceToHost));
+        NB_CUDA(ctx, cudaMemcpy(&b, st->flag_blk + ((n - 2) >> SCAN_SHIFT), 4, cudaMemcpyDeviceToHost));
+        nodes = a + b;
+    }
+    counters[0] = (int64_t)c[0]; counters[1] = (int64_t)c[1]; counters[2] = (int64_t)c[2]; counters[3] = (int64_t)c[3];
+    counters[4] = nodes; counters[5] = (int64_t)c[4];
+    return NB_OK;
 }
-}
+
+}  // extern "C"
