@@ -1,0 +1,213 @@
+"""GPU parity tests of the Barnes-Hut pipeline, stage by stage, through the C ABI."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+EPS = 1.01
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CASES = ["disk_8192", "disk_5000_ragged", "clustered_8192", "tight_clusters_4097", "duplicates_3000",
+         "two_galaxies_6000", "tiny_2", "tiny_3", "tiny_33"]
+
+
+def _cases(pkg):
+    dup = pkg.ics.uniform_disk(3000, seed=31)
+    dup[100:140, :2] = dup[99, :2]            # 41 coincident bodies -> depth-cap bucket
+    dup[2000:2003, :2] = dup[1999, :2]
+    return {
+        "disk_8192": pkg.ics.uniform_disk(8192, seed=1),
+        "disk_5000_ragged": pkg.ics.uniform_disk(5000, seed=32),
+        "clustered_8192": pkg.ics.clustered(8192, seed=5, sigma=300.0),
+        "tight_clusters_4097": pkg.ics.clustered(4097, seed=6, sigma=0.5, clusters=3),
+        "duplicates_3000": dup,
+        "two_galaxies_6000": pkg.ics.two_galaxies(6000),
+        "tiny_2": pkg.ics.uniform_disk(2, seed=33),
+        "tiny_3": pkg.ics.uniform_disk(3, seed=34),
+        "tiny_33": pkg.ics.uniform_disk(33, seed=35),
+    }
+
+
+def _dev(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _rel(a, b):
+    return (np.linalg.norm(a[:, :2].astype(np.float64) - b[:, :2], axis=1)
+            / np.maximum(np.linalg.norm(b[:, :2], axis=1), 1e-30))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_integer_stages_bit_exact(engine, pkg, oracle, case):
+    """bounds, SFC keys, sort permutation, tree keys: bit-exact against the oracle (itself pinned to the
+    reference's kernels by tests/golden)."""
+    pos = _cases(pkg)[case]
+    st = engine.bh_stages(_dev(pos))
+    b = oracle.bh_bounds(pos)
+    assert np.array_equal(st["bounds"], b)
+    k = oracle.bh_keys(pos, b)
+    assert np.array_equal(st["keys"], k)
+    _, si = oracle.sort_pairs(k)
+    assert np.array_equal(st["sorted_idx"], si)
+    assert np.array_equal(st["tree_keys"], oracle.bh_tree_keys(pos, b))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_tree_topology_and_accelerations(engine, pkg, oracle, case):
+    import torch
+    pos = _cases(pkg)[case]
+    n = pos.shape[0]
+    theta = 0.5
+    acc = torch.full((n, 4), 7.0, device="cuda")
+    engine.bh_accel(_dev(pos), acc, theta, EPS, pkg.NB_BH_COUNT_WALK)
+    torch.cuda.synchronize()
+    got = acc.cpu().numpy()
+    # topology: identical set of cells (prefix, level, count); monopoles in FP64 on both sides
+    c = engine.bh_export_tree()
+    b = oracle.bh_bounds(pos)
+    _, si = oracle.sort_pairs(oracle.bh_keys(pos, b))
+    t = oracle.Tree(pos, b, si)
+    oc = t.canonical()
+    assert np.array_equal(c["prefix"], oc["prefix"])
+    assert np.array_equal(c["level"], oc["level"])
+    assert np.array_equal(c["count"], oc["count"])
+    assert np.allclose(c["mass"], oc["mass"], rtol=1e-12)
+    scale = np.abs(pos[:, :2]).max()
+    assert np.abs(c["cx"] - oc["cx"]).max() < 1e-9 * scale and np.abs(c["cy"] - oc["cy"]).max() < 1e-9 * scale
+    # accelerations: same interaction lists as the oracle walk, FP32 rounding only
+    oa, cnt = t.walk(si, theta, EPS)
+    assert np.all(got[:, 2:] == 0)
+    e = _rel(got, oa.astype(np.float64))
+    assert np.median(e) < 2e-6 and np.quantile(e, 0.99) < 2e-5, (np.median(e), np.quantile(e, 0.99), e.max())
+    k = engine.bh_last_counters()
+    assert abs(k["interactions"] - cnt["interactions"]) <= 1e-4 * cnt["interactions"] + 64
+    assert k["status"] == 0
+
+
+@pytest.mark.parametrize("name", ["bh_disk_n8192", "bh_disk_n16384_t04", "bh_clustered_n8192"])
+def test_against_reference_golden(engine, pkg, name):
+    """Outputs of the reference's own kernels on B200 (tests/golden): integer stages bit-exact, topology
+    identical, accelerations equal up to the reference's float-atomic centre-of-mass noise."""
+    import torch
+    g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    pos = g["pos"]
+    n = pos.shape[0]
+    st = engine.bh_stages(_dev(pos))
+    assert np.array_equal(st["bounds"], g["bounds"])
+    assert np.array_equal(st["sorted_idx"], g["sorted_idx"])
+    assert np.array_equal(st["keys"][g["sorted_idx"]], g["sorted_keys"])
+    acc = torch.zeros(n, 4, device="cuda")
+    engine.bh_accel(_dev(pos), acc, float(g["theta"]), float(g["eps"]))
+    torch.cuda.synchronize()
+    c = engine.bh_export_tree()
+    assert np.array_equal(c["prefix"], g["cell_prefix"])
+    assert np.array_equal(c["level"], g["cell_level"])
+    assert np.array_equal(c["count"], g["cell_count"])
+    e = _rel(acc.cpu().numpy(), g["acc"].astype(np.float64))
+    assert np.median(e) < 5e-6 and np.quantile(e, 0.99) < 1e-3, (np.median(e), np.quantile(e, 0.99), e.max())
+
+
+def test_theta_error_distribution_matches_oracle(engine, pkg, oracle):
+    """theta-error against the FP64 direct sum: same distribution as the reference algorithm (oracle)."""
+    import torch
+    n = 16384
+    pos = pkg.ics.uniform_disk(n, seed=41)
+    d = oracle.direct_f64(pos, 2, EPS)
+    for theta in (0.3, 0.5, 0.8):
+        acc = torch.zeros(n, 4, device="cuda")
+        engine.bh_accel(_dev(pos), acc, theta, EPS)
+        torch.cuda.synchronize()
+        e_gpu = _rel(acc.cpu().numpy(), d)
+        e_ora = _rel(oracle.bh_accel(pos, theta, EPS)["acc"], d)
+        for q in (0.5, 0.99):
+            assert abs(np.quantile(e_gpu, q) - np.quantile(e_ora, q)) <= 0.02 * np.quantile(e_ora, q) + 1e-7
+        assert e_gpu.max() <= 1.05 * e_ora.max() + 1e-6
+
+
+def test_small_theta_converges_to_direct_sum(engine, pkg, oracle):
+    import torch
+    pos = pkg.ics.uniform_disk(4096, seed=42)
+    acc = torch.zeros(4096, 4, device="cuda")
+    engine.bh_accel(_dev(pos), acc, 1e-4, EPS)
+    torch.cuda.synchronize()
+    d = oracle.direct_f64(pos, 2, EPS)
+    assert _rel(acc.cpu().numpy(), d).max() < 5e-5
+
+
+def test_group_slices_tile_the_full_result(engine, pkg):
+    import torch
+    n = 10000
+    pos = _dev(pkg.ics.uniform_disk(n, seed=43))
+    full = torch.zeros(n, 4, device="cuda")
+    engine.bh_accel(pos, full, 0.5, EPS)
+    parts = torch.full((n, 4), -1.0, device="cuda")
+    groups = (n + 31) // 32
+    cuts = [0, 1, 100, 101, groups - 1, groups]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        engine.bh_accel_groups(pos, parts, 0.5, EPS, a, b - a)
+    torch.cuda.synchronize()
+    assert torch.equal(full, parts)
+
+
+def test_deterministic_and_single_body(engine, pkg):
+    import torch
+    pos = _dev(pkg.ics.clustered(20000, seed=44, sigma=50.0))
+    a = torch.zeros(20000, 4, device="cuda")
+    b = torch.zeros(20000, 4, device="cuda")
+    engine.bh_accel(pos, a, 0.5, EPS)
+    engine.bh_accel(pos, b, 0.5, EPS)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    one = _dev(np.array([[1, 2, 0, 3]], np.float32))
+    acc = torch.full((1, 4), 5.0, device="cuda")
+    engine.bh_accel(one, acc, 0.5, EPS)
+    torch.cuda.synchronize()
+    assert torch.all(acc == 0)
+
+
+def test_accumulate_bounds_flag(pkg, oracle):
+    """NB_BH_ACCUMULATE_BOUNDS reproduces the reference's never-reset d_bounds (running union)."""
+    big = pkg.ics.uniform_disk(4096, seed=45, radius=30000.0)
+    small = pkg.ics.uniform_disk(4096, seed=46, radius=1000.0)
+    eng = pkg.Engine(0, 4096)
+    b1 = eng.bh_stages(_dev(big), pkg.NB_BH_ACCUMULATE_BOUNDS)["bounds"]
+    b2 = eng.bh_stages(_dev(small), pkg.NB_BH_ACCUMULATE_BOUNDS)["bounds"]
+    assert np.array_equal(b1, oracle.bh_bounds(big))
+    assert np.array_equal(b2, oracle.bh_bounds(small, prev=b1)) and np.array_equal(b2, b1)
+    b3 = eng.bh_stages(_dev(small))["bounds"]
+    assert np.array_equal(b3, oracle.bh_bounds(small))
+    eng.close()
+
+
+def test_host_entry_point(engine, pkg, oracle):
+    pos = pkg.ics.uniform_disk(8192, seed=47)
+    got = engine.bh_accel_host(pos, 0.5, EPS)
+    o = oracle.bh_accel(pos, 0.5, EPS)
+    assert np.median(_rel(got, o["acc"].astype(np.float64))) < 2e-6
+
+
+def test_large_n_properties(pkg, oracle):
+    """N = 1,048,576 (BASELINE.json size): sortedness of the key array, permutation validity, stability,
+    and accelerations of a sample of bodies against the FP64 direct sum."""
+    import torch
+    n = 1 << 20
+    eng = pkg.Engine(0, n)
+    pos = pkg.ics.uniform_disk(n, seed=1)
+    dpos = _dev(pos)
+    st = eng.bh_stages(dpos)
+    si = st["sorted_idx"]
+    assert np.array_equal(np.sort(si), np.arange(n, dtype=np.int32))
+    sk = st["keys"][si]
+    assert np.all(sk[1:] >= sk[:-1])
+    ties = sk[1:] == sk[:-1]
+    assert np.all(si[1:][ties] > si[:-1][ties])          # stable: ties keep index order
+    acc = torch.zeros(n, 4, device="cuda")
+    eng.bh_accel(dpos, acc, 0.5, EPS)
+    torch.cuda.synchronize()
+    sample = np.arange(0, n, n // 512)[:512]
+    got = acc.cpu().numpy()[sample]
+    ref = np.concatenate([oracle.direct_f64(pos, 2, EPS, t0=int(t), nt=1) for t in sample])
+    e = _rel(got, ref)
+    assert np.median(e) < 2e-3 and e.max() < 0.05, (np.median(e), e.max())
+    eng.close()
