@@ -299,19 +299,81 @@ def main():
             extra["reference_cuda_kernel"] = {"interactions_per_s": interactions / (ref_ms * 1e-3), "ms": ref_ms,
                                               "what": "unmodified src/DirectComputeKernels.cu built for sm_100, same box"}
 
-    # ---- Barnes-Hut metric ---------------------------------------------------------------------------------
+    # ---- Barnes-Hut metric (configs[2]: N = 1,048,576, theta = 0.5, one force evaluation per Leapfrog step) ------
     if not args.skip_bh:
         try:
-            p2 = torch.from_numpy(pkg.ics.uniform_disk(N_BODIES, seed=1)).to(dev)
-            a2 = torch.zeros(N_BODIES, 4, device=dev)
-            groups = (N_BODIES + 31) // 32
+            nb = N_BODIES
+            p2_h = pkg.ics.uniform_disk(nb, seed=1)
+            p2 = torch.from_numpy(p2_h).to(dev)
+            a2 = torch.zeros(nb, 4, device=dev)
+            groups = (nb + 31) // 32
             g0, g1 = (groups * rank) // world, (groups * (rank + 1)) // world
 
             def bh_step():
                 eng.bh_accel_groups(p2, a2, THETA, EPS, g0, g1 - g0)
-            bh_ms = timed(bh_step, max(args.steps, 10), 3) / max(args.steps, 10)
-            extra["bh"] = {"metric": "BH steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
-                           "ms_per_step": bh_ms, "counters": eng.bh_last_counters() if rank == 0 else None}
+            ksteps = max(args.steps, 10)
+            bh_ms = timed(bh_step, ksteps, 3) / ksteps
+            bh = {"metric": "BH steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
+                  "ms_per_step": bh_ms, "n": nb, "theta": THETA}
+            if rank == 0:
+                eng.bh_accel_groups(p2, a2, THETA, EPS, 0, groups, flags=pkg.NB_BH_COUNT_WALK)
+                cnt = eng.bh_last_counters()
+                b_lin = 144.0 * nb + 32.0 * cnt["nodes"]
+                b_walk = 16.0 * (cnt["opened"] + cnt["examined"])
+                bh["counters"] = cnt
+                if world == 1:
+                    gbs = (b_lin + b_walk) / (bh_ms * 1e-3) / 1e9
+                    peak = 6551.0
+                    try:
+                        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+                        src = "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+                    except Exception:
+                        src = "fallback 6551 GB/s (MEASURED_PEAKS.json absent on this box)"
+                    bh["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                                      "traffic": None, "algorithmic_bytes": b_lin + b_walk, "b_lin": b_lin,
+                                      "b_walk": b_walk, "peak_source": src,
+                                      "lane_interactions_per_s": cnt["interactions"] / (bh_ms * 1e-3)}
+                    # end to end through the host-buffer entry point
+                    p2_pin = torch.from_numpy(p2_h).pin_memory()
+                    a2_pin = torch.empty(nb, 4).pin_memory()
+                    for _ in range(2):
+                        eng.bh_accel_host(p2_pin, THETA, EPS, out=a2_pin)
+                    t0 = time.perf_counter()
+                    for _ in range(ksteps):
+                        eng.bh_accel_host(p2_pin, THETA, EPS, out=a2_pin)
+                    bh["e2e"] = {"value": ksteps / (time.perf_counter() - t0), "unit": "steps/s",
+                                 "h2d_bytes_per_step": nb * 16, "d2h_bytes_per_step": nb * 16,
+                                 "call": "nb_bh_accel_host"}
+                    so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
+                    if os.path.exists(so) and not args.skip_refcuda:
+                        import ctypes as C
+                        ref = C.CDLL(so)
+                        vp = C.c_void_p
+                        ref.ref_barnes_hut.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_float]
+                        m = 3 * nb
+                        rp = torch.zeros(m, 4, device=dev)
+                        rp[:nb] = p2
+                        ra = torch.zeros(nb, 4, device=dev)
+                        fmax = float(np.finfo(np.float32).max)
+                        rb = torch.tensor([fmax, fmax, -fmax, -fmax], device=dev)
+                        ri = torch.zeros(1, dtype=torch.int32, device=dev)
+                        rn = torch.zeros(4 * m, dtype=torch.int32, device=dev)
+                        rs = torch.zeros(nb, dtype=torch.int32, device=dev)
+                        rk = torch.zeros(nb, dtype=torch.int32, device=dev)
+                        tms = []
+                        for _ in range(4):
+                            torch.cuda.synchronize()
+                            t0 = time.perf_counter()
+                            ref.ref_barnes_hut(rp.data_ptr(), ra.data_ptr(), rb.data_ptr(), ri.data_ptr(), rn.data_ptr(),
+                                               rs.data_ptr(), rk.data_ptr(), nb, m, THETA, EPS)   # synchronises itself
+                            tms.append((time.perf_counter() - t0) * 1e3)
+                        ref_ms = min(tms[1:])
+                        d = (ra[:, :2] - a2[:, :2]).norm(dim=1) / ra[:, :2].norm(dim=1)
+                        bh["reference_cuda_bh"] = {"steps_per_s": 1e3 / ref_ms, "ms": ref_ms, "speedup": ref_ms / bh_ms,
+                                                   "acc_rel_diff_median": float(d.median()),
+                                                   "acc_rel_diff_p99": float(d.quantile(0.99)),
+                                                   "what": "unmodified src/BarnesHutKernels.cu (sm_100), knodes=3, same box"}
+            extra["bh"] = bh
         except pkg.NbodyError as e:
             extra["bh"] = {"unavailable": str(e)}
 
