@@ -40,6 +40,7 @@ extern "C" {
 #define NB_ERR_CUDA 2      /* a CUDA runtime call failed; see nb_last_error */
 #define NB_ERR_OVERFLOW 3  /* a device-side capacity was exceeded (tree node pool, traversal stack) */
 #define NB_ERR_NO_DEVICE 4
+#define NB_ERR_TOO_LARGE 5  /* problem size beyond a fixed capacity (nb_direct_accel_noalloc) */
 
 /* flags for nb_direct_accel* */
 #define NB_DIRECT_AUTO 0      /* split the source range across CTAs when that fills the GPU better */
@@ -89,6 +90,18 @@ int nb_direct_accel_slice(nb_context* ctx, const float* pos, int n, int target_b
  * + updateHostData do around the reference kernels (src/NbodySystem.cpp:70-93). */
 int nb_direct_accel_host(nb_context* ctx, const float* host_pos, float* host_acc, int n, int dim,
                          float softening, int flags);
+
+/* No counterpart in the reference.  The same direct sum for callers that must not allocate device memory --
+ * a host whose time loop has already claimed the GPU's memory, or whose step may never run into the
+ * device-wide synchronisation of cudaMalloc/cudaFree.  Takes no handle and calls no allocator: the partial
+ * sums of the split-source kernel live in a fixed 16 MiB array inside the library (every GPU that loads it
+ * holds that array until exit).  n <= NB_NOALLOC_MAX_BODIES, else NB_ERR_TOO_LARGE (text via
+ * nb_last_error(NULL)).  Runs on the CURRENT device, on `stream`.  All calls share the array and it keeps the
+ * last call's partials (nothing in it needs clearing: each call overwrites what it reads), so calls that
+ * can overlap on the GPU race -- serialise them.  The first call on a device looks up the array's device
+ * address; make that call before any stream capture. */
+#define NB_NOALLOC_MAX_BODIES 262144
+int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int dim, float softening, void* stream);
 
 /* Number of source-range splits (1 = ordered) and thread blocks the last direct call used. */
 int nb_direct_last_launch(const nb_context* ctx, int* jsplit, int* blocks, int* launches);

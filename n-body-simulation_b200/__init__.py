@@ -22,7 +22,8 @@ NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS, NB_BH_COUNT_WALK = 0, 1, 0x100
 # every symbol include/nbody_b200.h declares (tests check that the library exports each one)
 ABI_SYMBOLS = [
     "nb_create", "nb_destroy", "nb_last_error", "nb_device_info",
-    "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_last_launch",
+    "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_accel_noalloc",
+    "nb_direct_last_launch",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
 ]

@@ -267,3 +267,116 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     ctx->last_launches = launches;
     return NB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------
+// nb_direct_accel_noalloc -- the split-source direct sum for callers that are not allowed to allocate.
+//
+// Some hosts of this library cannot call cudaMalloc once their time loop is running: a simulation that has
+// already handed every free byte of device memory to its own pools, a real-time or in-situ driver whose
+// step must never hit the implicit device-wide synchronisation of cudaMalloc/cudaFree, or a plug-in that is
+// only given a stream and two device pointers and no right to own memory.  For them the partial sums of the
+// split-source kernel live in the fixed array below, which is part of the loaded module: every GPU that
+// loads libnbody_b200.so carries these 16 MiB until the process exits.
+//
+//   * limit: n <= NB_NOALLOC_MAX_BODIES (262,144); larger systems are refused with NB_ERR_TOO_LARGE;
+//   * nothing in the array has to start at zero -- every partial that the reduction reads is written by the
+//     force kernel of the same call -- so no clearing pass is launched;
+//   * all calls share the one array and it keeps the previous call's partials: two calls whose kernels can
+//     overlap on the GPU (different streams, no dependency) race; serialise them;
+//   * the first call on each device looks up the array's device address and raises the kernel's shared-memory
+//     limit; make that first call outside any stream capture.  The device that is current at the call is used.
+// ------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)16 << 20;
+constexpr int NOALLOC_MAX_PARTIALS = (int)(NOALLOC_SCRATCH_BYTES / sizeof(float4));   // 1,048,576 float4
+constexpr int NOALLOC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+struct NoAllocDevice {
+    bool ready = false;
+    float4* scratch = nullptr;   // device address of g_noalloc_scratch on this device
+    int sm_count = 0;
+    int occupancy[2] = {0, 0};   // [dim - 2]
+};
+NoAllocDevice g_noalloc_dev[NOALLOC_MAX_DEVICES];
+std::mutex g_noalloc_mutex;
+
+int noalloc_fail(int code, const char* what, cudaError_t e = cudaSuccess) { return nb_fail(nullptr, code, what, e); }
+
+}  // namespace
+
+extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int dim, float softening, void* stream) {
+    if (dim != 2 && dim != 3) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: dim must be 2 or 3");
+    if (n < 0) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: n must be >= 0");
+    if (n > NB_NOALLOC_MAX_BODIES)
+        return noalloc_fail(NB_ERR_TOO_LARGE,
+                            "nb_direct_accel_noalloc: n exceeds NB_NOALLOC_MAX_BODIES (262144), the static scratch "
+                            "cannot hold the partial sums; use nb_direct_accel");
+    if (n == 0) return NB_OK;
+    if (!pos || !acc) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: null device pointer");
+
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return noalloc_fail(NB_ERR_NO_DEVICE, "nb_direct_accel_noalloc: cudaGetDevice", e);
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: device index");
+    NoAllocDevice& d = g_noalloc_dev[dev];
+    kernel_fn fn = dim == 2 ? (kernel_fn)direct_kernel<2, 2, 3> : (kernel_fn)direct_kernel<3, 2, 3>;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!d.ready) {
+            // once per device, with that device current: the symbol's name is only a host-side stand-in, the
+            // kernel needs the address the array has on THIS device
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaGetSymbolAddress", e);
+            e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev);
+            if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaDeviceGetAttribute", e);
+            kernel_fn fns[2] = {(kernel_fn)direct_kernel<2, 2, 3>, (kernel_fn)direct_kernel<3, 2, 3>};
+            for (int k = 0; k < 2; k++) {
+                e = cudaFuncSetAttribute(fns[k], cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+                if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaFuncSetAttribute", e);
+                int occ = 0;
+                e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fns[k], NT, SMEM_BYTES);
+                if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: occupancy query", e);
+                d.occupancy[k] = occ > 0 ? occ : 1;
+            }
+            d.scratch = reinterpret_cast<float4*>(p);
+            d.ready = true;
+        }
+    }
+
+    // same wave-filling rule as nb_direct_accel, bounded by what the static array can hold
+    const int ntiles = (n + TILE - 1) / TILE;
+    const int per_block = NT * 2 * 2;
+    const int tblocks = (n + per_block - 1) / per_block;
+    const int slots = d.sm_count * d.occupancy[dim - 2];
+    int max_js = ntiles / 2;
+    if (max_js > 64) max_js = 64;
+    if (max_js > NOALLOC_MAX_PARTIALS / n) max_js = NOALLOC_MAX_PARTIALS / n;
+    if (max_js < 1) max_js = 1;
+    int jsplit = 1;
+    double best = -1.0;
+    for (int js = 1; js <= max_js; js++) {
+        const long long blocks = (long long)tblocks * js;
+        const long long waves = (blocks + slots - 1) / slots;
+        const double eff = (double)blocks / (double)(waves * slots);
+        if (eff > best + 1e-9) {
+            best = eff;
+            jsplit = js;
+        }
+        if (eff >= 0.97) break;
+    }
+
+    cudaStream_t s = (cudaStream_t)stream;
+    float4* out = jsplit > 1 ? d.scratch : reinterpret_cast<float4*>(acc);
+    fn<<<dim3(tblocks, jsplit), NT, SMEM_BYTES, s>>>(reinterpret_cast<const float4*>(pos), n, 0, n, softening, out, jsplit);
+    if (jsplit > 1)
+        reduce_partials_kernel<<<(n + 255) / 256, 256, 0, s>>>(d.scratch, n, jsplit, reinterpret_cast<float4*>(acc));
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: kernel launch", e);
+    return NB_OK;
+}
