@@ -30,7 +30,8 @@ namespace {
 constexpr int MAX_LEVEL = 32;             // depth cap: 32 levels of bisection = 64-bit keys; deeper cells become buckets
 constexpr uint32_t LINK_EMPTY = 0xFFFFFFFFu;
 constexpr uint32_t LINK_BODY = 0xFFFFFFFEu;
-constexpr uint32_t KIND_BUCKET = 63u;     // link = (level << 26) | node id ; level field 63 marks a bucket node
+constexpr uint32_t LINK_BUCKET = 0x80000000u;  // link = node id, bit 31 set when the node is a depth-cap bucket
+constexpr float FAR_AWAY = 3.0e18f;            // position of an empty slot: zero mass, contributes exactly 0
 constexpr int WALK_STACK = 128;           // >= 3 * 33 + 1
 
 struct D3 {
@@ -52,13 +53,15 @@ struct nb_bh_state {
     int32_t* idx64[2] = {nullptr, nullptr};
     uint32_t* hist = nullptr;          // radix histograms [256][blocks]
     size_t hist_elems = 0;
+    uint32_t* digit_total = nullptr;   // [256]
     float4* spos = nullptr;            // bodies in tree order: (x, y, m, -)
     D3* psum = nullptr;                // chunk-local inclusive prefix sums of (m, m x, m y)
     D3* psum_blk = nullptr;            // exclusive prefix of the chunk totals
     int32_t* left = nullptr;           // per boundary: left extent of its node
     int32_t* flag_scan = nullptr;      // chunk-local inclusive scan of leader flags
     int32_t* flag_blk = nullptr;
-    float4* cblk = nullptr;            // child blocks, 4 x float4 per node
+    float4* cblk = nullptr;            // child blocks, 4 x (cx, cy, m, acceptance threshold) per node
+    uint4* clink = nullptr;            // the four child links of a node (LINK_EMPTY / LINK_BODY / bucket flag | node id)
     int32_t* node_first = nullptr;
     int32_t* node_last = nullptr;
     int8_t* node_level = nullptr;
@@ -208,61 +211,61 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_hist_kernel(const K* __rest
     hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];  // digit-major
 }
 
-// exclusive scan of `count` uint32 in place, one block (count = 256 * nblocks)
-__global__ void __launch_bounds__(1024) scan_u32_kernel(uint32_t* __restrict__ data, int count) {
-    __shared__ uint32_t wsum[32];
-    __shared__ uint32_t carry_s;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
-    const int per = 8;
-    for (int base = 0; base < count; base += 1024 * per) {
-        uint32_t v[per];
-        uint32_t s = 0;
-        const int i0 = base + threadIdx.x * per;
-#pragma unroll
-        for (int k = 0; k < per; k++) {
-            v[k] = (i0 + k < count) ? data[i0 + k] : 0u;
-            s += v[k];
-        }
-        uint32_t inc = s;
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-            if ((threadIdx.x & 31) >= o) inc += t;
-        }
-        if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            uint32_t w = wsum[threadIdx.x];
-            uint32_t winc = w;
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
-                if (threadIdx.x >= o) winc += t;
-            }
-            wsum[threadIdx.x] = winc - w;  // exclusive over warps
-        }
-        __syncthreads();
-        uint32_t run = carry_s + wsum[threadIdx.x >> 5] + (inc - s);
-#pragma unroll
-        for (int k = 0; k < per; k++) {
-            if (i0 + k < count) data[i0 + k] = run;
-            run += v[k];
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) carry_s = run;
-        __syncthreads();
+// Block d turns row d of the digit-major histogram (one count per sort tile) into an exclusive prefix over
+// the tiles and stores the row total; the digit bases are added by the scatter kernel.
+__global__ void __launch_bounds__(256) scan_rows_kernel(uint32_t* __restrict__ hist, int nblocks,
+                                                       uint32_t* __restrict__ digit_total) {
+    __shared__ uint32_t wsum[8];
+    uint32_t* row = hist + (size_t)blockIdx.x * nblocks;
+    const int per = (nblocks + 255) / 256;
+    const int i0 = threadIdx.x * per;
+    uint32_t s = 0;
+    for (int k = 0; k < per; k++) s += (i0 + k < nblocks) ? row[i0 + k] : 0u;
+    uint32_t inc = s;
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if ((threadIdx.x & 31) >= o) inc += t;
     }
+    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    uint32_t run = inc - s;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) run += wsum[w];
+    for (int k = 0; k < per; k++) {
+        if (i0 + k < nblocks) {
+            const uint32_t v = row[i0 + k];
+            row[i0 + k] = run;
+            run += v;
+        }
+    }
+    if (threadIdx.x == 255) digit_total[blockIdx.x] = run;
 }
 
 template <typename K>
 __global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __restrict__ keys_in,
                                                                    const int32_t* __restrict__ vals_in, int n, int shift,
                                                                    const uint32_t* __restrict__ offs, int nblocks,
+                                                                   const uint32_t* __restrict__ digit_total,
                                                                    K* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
     // tile order = warp-major, round-major, lane: warp w owns keys [w*512, (w+1)*512) of the tile
     constexpr int WARPS = SORT_THREADS / 32;
     __shared__ uint32_t cnt[WARPS][256];
+    __shared__ uint32_t dbase[256];
+    __shared__ uint32_t dw[WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int d = lane; d < 256; d += 32) cnt[warp][d] = 0;
+    {   // exclusive prefix of the 256 digit totals = where each digit's bin starts in the output
+        const uint32_t v = digit_total[threadIdx.x];
+        uint32_t inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) dw[warp] = inc;
+        __syncthreads();
+        uint32_t off = inc - v;
+        for (int w = 0; w < warp; w++) off += dw[w];
+        dbase[threadIdx.x] = off;
+    }
     __syncwarp();
     const int wbase = blockIdx.x * SORT_TILE + warp * (32 * SORT_ITEMS);
     K key[SORT_ITEMS];
@@ -291,7 +294,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __r
     __syncthreads();
     {   // per digit: exclusive prefix over warps, plus the global offset of this block's digit bin
         const int d = threadIdx.x;
-        uint32_t run = offs[(size_t)d * nblocks + blockIdx.x];
+        uint32_t run = dbase[d] + offs[(size_t)d * nblocks + blockIdx.x];
 #pragma unroll
         for (int w = 0; w < WARPS; w++) {
             const uint32_t c = cnt[w][d];
@@ -319,9 +322,9 @@ int radix_sort(nb_context* ctx, nb_bh_state* st, K* keys[2], int32_t* vals[2], i
     int sel = 0;
     for (int shift = 0; shift < bits; shift += 8) {
         sort_hist_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], n, shift, st->hist, nblocks);
-        scan_u32_kernel<<<1, 1024, 0, stream>>>(st->hist, 256 * nblocks);
+        scan_rows_kernel<<<256, 256, 0, stream>>>(st->hist, nblocks, st->digit_total);
         sort_scatter_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], vals[sel], n, shift, st->hist, nblocks,
-                                                                    keys[sel ^ 1], vals[sel ^ 1]);
+                                                                    st->digit_total, keys[sel ^ 1], vals[sel ^ 1]);
         sel ^= 1;
     }
     *sel_out = sel;
@@ -501,11 +504,20 @@ __device__ __forceinline__ D3 prefix_incl(const TreeView& t, int i) {  // sum ov
 }
 __device__ __forceinline__ int flag_incl(const TreeView& t, int i) { return t.flag_scan[i] + t.flag_blk[i >> SCAN_SHIFT]; }
 
+// Acceptance threshold (squared size / theta^2) a cell that splits at level L is tested with:
+// s0 * 0.25^(L-1), s0 = (dim_size/theta)^2 (src/BarnesHutKernels.cu:403-404,411; the scaling is exact).
+// Level-0/1 cells are never tested (:398-407) -> +inf.  Bodies are always summed (:430) -> 0.
+__device__ __forceinline__ float threshold_of(float s0, int L) {
+    if (L < 2) return __int_as_float(0x7f800000);
+    return s0 * __int_as_float((127 - 2 * (L - 1)) << 23);
+}
+
 __global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __restrict__ left,
-                                                  float4* __restrict__ cblk, int32_t* __restrict__ node_first,
-                                                  int32_t* __restrict__ node_last, int8_t* __restrict__ node_level,
-                                                  int8_t* __restrict__ node_top, int32_t* __restrict__ root,
-                                                  float4* __restrict__ root_rec) {
+                                                  const float4* __restrict__ bounds, float theta,
+                                                  float4* __restrict__ cblk, uint4* __restrict__ clink,
+                                                  int32_t* __restrict__ node_first, int32_t* __restrict__ node_last,
+                                                  int8_t* __restrict__ node_level, int8_t* __restrict__ node_top,
+                                                  int32_t* __restrict__ root, float4* __restrict__ root_rec) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= t.n - 1) return;
     const int incl = flag_incl(t, i);
@@ -519,14 +531,18 @@ __global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __
     node_first[id] = a;
     node_last[id] = b;
     node_level[id] = (int8_t)L;
+    const float4 bb = *bounds;
+    const float dim_size = fmaxf(bb.z - bb.x, bb.w - bb.y);       // src/BarnesHutKernels.cu:384
+    float s0 = dim_size / theta;                                   // :403
+    s0 *= s0;                                                      // :404
     if (a == 0 && b == t.n - 1) {
         root[0] = id;
         node_top[id] = 0;
         const D3 all = prefix_incl(t, t.n - 1);
         float cx = 0.f, cy = 0.f;
         if (all.m > 0.0) { cx = (float)(all.mx / all.m); cy = (float)(all.my / all.m); }
-        const uint32_t lev = L >= MAX_LEVEL ? KIND_BUCKET : (uint32_t)L;
-        *root_rec = make_float4(cx, cy, (float)all.m, __uint_as_float((lev << 26) | (uint32_t)id));
+        root_rec[0] = make_float4(cx, cy, (float)all.m, threshold_of(s0, L));
+        root_rec[1] = make_float4(__uint_as_float((uint32_t)id | (L >= MAX_LEVEL ? LINK_BUCKET : 0u)), 0.f, 0.f, 0.f);
     }
     float4* blk = cblk + 4 * (size_t)id;
     if (L >= MAX_LEVEL) {  // bucket: all keys equal; the walk sums bodies [a, b] directly
@@ -534,16 +550,22 @@ __global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __
         return;
     }
     float4 rec[4];
+    uint32_t lk[4];
 #pragma unroll
-    for (int s = 0; s < 4; s++) rec[s] = make_float4(0.f, 0.f, 0.f, __uint_as_float(LINK_EMPTY));
+    for (int s = 0; s < 4; s++) {
+        rec[s] = make_float4(FAR_AWAY, FAR_AWAY, 0.f, 0.f);   // empty: massless, always "accepted", adds exactly 0
+        lk[s] = LINK_EMPTY;
+    }
     int c0 = a;
     while (c0 <= b) {
         const int e = right_extent(K, c0, b, L + 1);
         const int slot = (int)((K[c0] >> (62 - 2 * L)) & 3ull) ^ 2;   // path = digit ^ 2
         float4 r;
+        uint32_t link;
         if (e == c0) {
             const float4 p = t.spos[c0];
-            r = make_float4(p.x, p.y, p.z, __uint_as_float(LINK_BODY));
+            r = make_float4(p.x, p.y, p.z, 0.f);
+            link = LINK_BODY;
         } else {
             const D3 hi = prefix_incl(t, e);
             D3 lo = D3{0.0, 0.0, 0.0};
@@ -555,15 +577,16 @@ __global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __
             const int e1 = right_extent(K, c0, e, Lc + 1);            // end of the child's first child = its leader boundary
             const int cid = flag_incl(t, e1) - 1;
             node_top[cid] = (int8_t)(L + 1);
-            const uint32_t lev = Lc >= MAX_LEVEL ? KIND_BUCKET : (uint32_t)Lc;
-            r = make_float4(cx, cy, (float)m, __uint_as_float((lev << 26) | (uint32_t)cid));
+            r = make_float4(cx, cy, (float)m, threshold_of(s0, Lc));
+            link = (uint32_t)cid | (Lc >= MAX_LEVEL ? LINK_BUCKET : 0u);
         }
 #pragma unroll
-        for (int s = 0; s < 4; s++) if (s == slot) rec[s] = r;
+        for (int s = 0; s < 4; s++) if (s == slot) { rec[s] = r; lk[s] = link; }
         c0 = e + 1;
     }
 #pragma unroll
     for (int s = 0; s < 4; s++) blk[s] = rec[s];
+    clink[id] = make_uint4(lk[0], lk[1], lk[2], lk[3]);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -571,12 +594,18 @@ __global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __
 // ------------------------------------------------------------------------------------------------------
 constexpr int WALK_WARPS = 8;
 
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __restrict__ pos,
                                                               const int32_t* __restrict__ sorted_idx, int n,
-                                                              const float4* __restrict__ cblk, const float4* __restrict__ spos,
-                                                              const float4* __restrict__ root_rec,
-                                                              const float4* __restrict__ bounds, float theta, float eps,
+                                                              const float4* __restrict__ cblk, const uint4* __restrict__ clink,
+                                                              const float4* __restrict__ spos,
+                                                              const float4* __restrict__ root_rec, float eps,
                                                               int group_begin, int group_count, float4* __restrict__ acc,
                                                               unsigned long long* __restrict__ counters) {
     __shared__ uint32_t stack_s[WALK_WARPS][WALK_STACK];
@@ -587,89 +616,67 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
     const bool valid = bi < n;
     const unsigned act = __ballot_sync(0xffffffffu, valid);
     if (!valid) return;
+    const int leader = __ffs(act) - 1;
     const int body = sorted_idx[bi];
     const float4 me = pos[body];
     const float x = me.x, y = me.y;
     float ax = 0.f, ay = 0.f;
     uint32_t* stack = stack_s[warp];
-
-    const float4 bb = *bounds;
-    const float dim_size = fmaxf(bb.z - bb.x, bb.w - bb.y);       // :384
-    float s0 = dim_size / theta;                                   // :403
-    s0 *= s0;                                                      // :404
     unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
     int c_depth = 0;
-    const int leader = __ffs(act) - 1;
 
-    auto interact = [&](float cx, float cy, float m) {
-        const float dx = cx - x, dy = cy - y;
-        const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
-        const float k = rsqrt_approx(r * r) * m;                   // :431
-        ax = __fmaf_rn(k, dx, ax);
-        ay = __fmaf_rn(k, dy, ay);
-    };
-    // size^2 threshold a cell that splits at level L is tested with: s0 * 0.25^(L-1)  (:411, exact scaling)
-    auto size_of = [&](int L) { return s0 * __int_as_float((127 - 2 * (L - 1)) << 23); };
-
-    // One candidate cell or body: sum it (body, or cell accepted by every target of the group) or push it.
-    auto consider = [&](const float4 c, int& wr) {
-        const uint32_t link = __float_as_uint(c.w);
-        if (link == LINK_EMPTY) return;
-        if (COUNT) c_exam++;
-        if (link == LINK_BODY) {                                   // child < n: always summed (:430)
-            interact(c.x, c.y, c.z);
-            if (COUNT) c_inter++;
-            return;
-        }
-        const uint32_t clev = link >> 26;
-        const int Lc = clev == KIND_BUCKET ? MAX_LEVEL : (int)clev;
+    // One candidate (cx, cy, m, thr): summed when every target of the group has thr <= r (src/BarnesHutKernels.cu:430;
+    // thr = 0 for bodies and empty slots, +inf for level-1 cells), pushed otherwise.  k = m / r  (:431).
+    auto consider = [&](const float4 c, const uint32_t link, int& wr) {
         const float dx = c.x - x, dy = c.y - y;
         const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
-        bool accept = false;
-        if (Lc >= 2) accept = __all_sync(act, size_of(Lc) <= r);   // :430; level-1 cells are never tested (:398-407)
-        if (accept) {
-            const float k = rsqrt_approx(r * r) * c.z;
+        if (__all_sync(act, c.w <= r)) {
+            const float k = rcp_approx(r) * c.z;
             ax = __fmaf_rn(k, dx, ax);
             ay = __fmaf_rn(k, dy, ay);
-            if (COUNT) c_inter++;
+            if (COUNT) { if (link != LINK_EMPTY) { c_exam++; c_inter++; } }
         } else {
             if (lane == leader) stack[wr] = link;
             wr++;
+            if (COUNT) c_exam++;
         }
     };
 
     int top;
     {
         int wr = 0;
-        consider(*root_rec, wr);
+        consider(root_rec[0], __float_as_uint(root_rec[1].x), wr);
         top = wr - 1;
     }
     __syncwarp(act);
     while (top >= 0) {
-        if (COUNT) { c_depth = max(c_depth, top + 1); }
+        if (COUNT) { c_depth = max(c_depth, top + 1); c_open++; }
         const uint32_t ent = stack[top];
         __syncwarp(act);
-        const uint32_t id = ent & 0x03FFFFFFu;
-        const uint32_t lev = ent >> 26;
+        const uint32_t id = ent & 0x7FFFFFFFu;
         const float4* blk = cblk + 4 * (size_t)id;
-        if (COUNT) c_open++;
-        if (lev == KIND_BUCKET) {
+        if (ent & LINK_BUCKET) {
             const float4 h = blk[0];
             const int first = __float_as_int(h.x), cnt = __float_as_int(h.y);
             for (int k = 0; k < cnt; k++) {
                 const float4 p = spos[first + k];
-                interact(p.x, p.y, p.z);
+                const float dx = p.x - x, dy = p.y - y;
+                const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+                const float kk = rcp_approx(r) * p.z;
+                ax = __fmaf_rn(kk, dx, ax);
+                ay = __fmaf_rn(kk, dy, ay);
             }
             if (COUNT) { c_exam += cnt; c_inter += cnt; }
             top--;
             continue;
         }
         const float4 r0 = blk[0], r1 = blk[1], r2 = blk[2], r3 = blk[3];
+        const uint4 lk = clink[id];
         int wr = top;  // the first rejected child overwrites the popped slot (:436-440), LIFO order
-        consider(r0, wr);
-        consider(r1, wr);
-        consider(r2, wr);
-        consider(r3, wr);
+        consider(r0, lk.x, wr);
+        consider(r1, lk.y, wr);
+        consider(r2, lk.z, wr);
+        consider(r3, lk.w, wr);
         __syncwarp(act);
         top = wr - 1;
     }
@@ -698,7 +705,7 @@ int alloc(nb_context* ctx, T** p, size_t count) {
 void free_state(nb_bh_state* st) {
     if (!st) return;
     void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
-                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->hist, st->spos, st->psum, st->psum_blk,
+                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->hist, st->digit_total, st->clink, st->spos, st->psum, st->psum_blk,
                     st->left, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
                     st->node_top, st->root, st->root_rec, st->counters};
     for (void* p : ptrs)
@@ -736,6 +743,7 @@ int ensure_state(nb_context* ctx, int n) {
     }
     st->hist_elems = 256 * sblocks;
     rc |= alloc(ctx, &st->hist, st->hist_elems);
+    rc |= alloc(ctx, &st->digit_total, 256);
     rc |= alloc(ctx, &st->spos, cap);
     rc |= alloc(ctx, &st->psum, cap);
     rc |= alloc(ctx, &st->psum_blk, chunks);
@@ -743,12 +751,13 @@ int ensure_state(nb_context* ctx, int n) {
     rc |= alloc(ctx, &st->flag_scan, cap);
     rc |= alloc(ctx, &st->flag_blk, chunks);
     rc |= alloc(ctx, &st->cblk, 4 * cap);
+    rc |= alloc(ctx, &st->clink, cap);
     rc |= alloc(ctx, &st->node_first, cap);
     rc |= alloc(ctx, &st->node_last, cap);
     rc |= alloc(ctx, &st->node_level, cap);
     rc |= alloc(ctx, &st->node_top, cap);
     rc |= alloc(ctx, &st->root, 2);
-    rc |= alloc(ctx, &st->root_rec, 1);
+    rc |= alloc(ctx, &st->root_rec, 2);
     rc |= alloc(ctx, &st->counters, 8);
     if (rc) return NB_ERR_CUDA;
     NB_CUDA(ctx, cudaMemset(st->ticket, 0, sizeof(unsigned int)));
@@ -762,7 +771,7 @@ int ensure_state(nb_context* ctx, int n) {
 }
 
 // stages: 1 = bounds, 2 = keys, 3 = sorts, 4 = tree
-int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, cudaStream_t stream) {
+int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, float theta, cudaStream_t stream) {
     int rc = ensure_state(ctx, n);
     if (rc) return rc;
     nb_bh_state* st = ctx->bh;
@@ -791,8 +800,9 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, cu
         boundary_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->left, st->flag_scan, st->flag_blk);
         scan_totals_kernel<int><<<1, 1024, 0, stream>>>(st->flag_blk, bchunks);
         TreeView tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, n};
-        emit_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->left, st->cblk, st->node_first, st->node_last,
-                                                             st->node_level, st->node_top, st->root, st->root_rec);
+        emit_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->left, st->bounds, theta, st->cblk, st->clink,
+                                                             st->node_first, st->node_last, st->node_level, st->node_top,
+                                                             st->root, st->root_rec);
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
@@ -811,13 +821,11 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
     const int blocks = (group_count + WALK_WARPS - 1) / WALK_WARPS;
     if (count) {
         cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
-        walk_kernel<true><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->spos, st->root_rec,
-                                                                 st->bounds, theta, eps, group_begin,
-                                                                 group_count, acc, st->counters);
+        walk_kernel<true><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
+                                                                 st->root_rec, eps, group_begin, group_count, acc, st->counters);
     } else {
-        walk_kernel<false><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->spos, st->root_rec,
-                                                                  st->bounds, theta, eps, group_begin,
-                                                                  group_count, acc, st->counters);
+        walk_kernel<false><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
+                                                                  st->root_rec, eps, group_begin, group_count, acc, st->counters);
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
@@ -855,7 +863,7 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)
         return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
-    rc = run_build(ctx, pos, n, flags, 4, (cudaStream_t)stream);
+    rc = run_build(ctx, pos, n, flags, 4, theta, (cudaStream_t)stream);
     if (rc) return rc;
     return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, (flags & NB_BH_COUNT_FLAG) != 0,
                     (cudaStream_t)stream);
@@ -891,7 +899,7 @@ int nb_bh_stages_host(nb_context* ctx, const float* pos, int n, int flags, float
     if (!ctx) return NB_ERR_INVALID;
     if (n <= 0 || !pos) return nb_fail(ctx, NB_ERR_INVALID, "need n > 0 and a device pointer");
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
-    int rc = run_build(ctx, pos, n, flags, 3, 0);
+    int rc = run_build(ctx, pos, n, flags, 3, 1.0f, 0);
     if (rc) return rc;
     nb_bh_state* st = ctx->bh;
     NB_CUDA(ctx, cudaDeviceSynchronize());
