@@ -155,23 +155,13 @@ def main():
 
     # ---- state: replicated positions, slice-local velocities / accelerations --------------------------
     pos_h = pkg.ics.uniform_disk(n, seed=1, z_half_height=3000.0 if dim == 3 else 0.0)
-    begin = (n * rank) // world
-    end = (n * (rank + 1)) // world
+    begin, end = pkg.shard.slice_bounds(n, world, rank)
     count = end - begin
     pos = torch.from_numpy(pos_h).to(dev)
     acc = torch.zeros(count, 4, device=dev)
     vel = torch.zeros(count, 4, device=dev)
-    equal = (n % world == 0)
-    sizes = [(n * (r + 1)) // world - (n * r) // world for r in range(world)]
-
     def gather_positions():
-        if world == 1:
-            return
-        if equal:
-            dist.all_gather_into_tensor(pos, pos[begin:end])       # in place, NCCL over NVLink
-        else:
-            outs = list(torch.split(pos, sizes, dim=0))
-            dist.all_gather(outs, pos[begin:end].clone())
+        pkg.shard.gather_positions(pos, n, world, rank, dist)     # one in-place NCCL all-gather over NVLink
 
     def force():
         eng.direct_accel_slice(pos, begin, count, acc, dim, EPS)
@@ -307,7 +297,7 @@ def main():
             p2 = torch.from_numpy(p2_h).to(dev)
             a2 = torch.zeros(nb, 4, device=dev)
             groups = (nb + 31) // 32
-            g0, g1 = (groups * rank) // world, (groups * (rank + 1)) // world
+            g0, g1 = pkg.shard.group_bounds(nb, world, rank)
 
             def bh_step():
                 eng.bh_accel_groups(p2, a2, THETA, EPS, g0, g1 - g0)

@@ -230,3 +230,4 @@ def _host_ptr(a):
 
 from .system import R2, R3, ComputeMethods, NbodySystem  # noqa: E402,F401
 from . import ics  # noqa: E402,F401
+from . import shard  # noqa: E402,F401

@@ -1,0 +1,46 @@
+"""torchrun --nproc-per-node G profiles/multigpu_check.py : sharded force evaluations against the single-GPU
+result on rank 0 (direct ordered mode: bit-identical; Barnes-Hut: bit-identical, the tree is rebuilt
+redundantly and the walk is deterministic)."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import __graft_entry__ as g  # noqa: E402
+
+pkg = g.load_package()
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+eng = pkg.Engine(local, 0)
+ok = True
+for n in (100000, 65536):
+    pos_h = pkg.ics.uniform_disk(n, seed=9, z_half_height=3000.0)
+    b, e = pkg.shard.slice_bounds(n, world, rank)
+    # every rank starts with only ITS slice valid; the all-gather must fill in the rest
+    pos = torch.zeros(n, 4, device="cuda")
+    pos[b:e] = torch.from_numpy(pos_h[b:e]).cuda()
+    pkg.shard.gather_positions(pos, n, world, rank, dist)
+    assert torch.equal(pos.cpu(), torch.from_numpy(pos_h)), "all-gather did not replicate the positions"
+    acc = torch.zeros(e - b, 4, device="cuda")
+    eng.direct_accel_slice(pos, b, e - b, acc, 3, 1.01, pkg.NB_DIRECT_ORDERED)
+    full = torch.zeros(n, 4, device="cuda")
+    eng.direct_accel(pos, full, 3, 1.01, pkg.NB_DIRECT_ORDERED)
+    ok &= bool(torch.equal(acc, full[b:e]))
+    # Barnes-Hut: sharded walk, then sum-reduce the (disjoint) contributions to compare with the full walk
+    pos2 = pos.clone()
+    pos2[:, 2] = 0
+    part = torch.zeros(n, 4, device="cuda")
+    g0, g1 = pkg.shard.group_bounds(n, world, rank)
+    eng.bh_accel_groups(pos2, part, 0.5, 1.01, g0, g1 - g0)
+    dist.all_reduce(part)
+    whole = torch.zeros(n, 4, device="cuda")
+    eng.bh_accel(pos2, whole, 0.5, 1.01)
+    ok &= bool(torch.equal(part, whole))
+t = torch.tensor([1 if ok else 0], device="cuda")
+dist.all_reduce(t, op=dist.ReduceOp.MIN)
+if rank == 0:
+    print("MULTIGPU_CHECK", "PASS" if int(t.item()) == 1 else "FAIL", "world", world)
+dist.destroy_process_group()
