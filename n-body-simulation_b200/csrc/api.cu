@@ -43,6 +43,7 @@ int nb_destroy(nb_context* ctx) {
     cudaDeviceSynchronize();
     nb_bh_destroy(ctx);
     if (ctx->partial) cudaFree(ctx->partial);
+    if (ctx->tile_flags) cudaFree(ctx->tile_flags);
     if (ctx->dev_pos) cudaFree(ctx->dev_pos);
     if (ctx->dev_acc) cudaFree(ctx->dev_acc);
     if (ctx->host_stream) cudaStreamDestroy(ctx->host_stream);
@@ -56,7 +57,7 @@ int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* 
     if (!ctx) return NB_ERR_INVALID;
     if (device) *device = ctx->device;
     if (sm_count) *sm_count = ctx->sm_count;
-    if (scratch_bytes) *scratch_bytes = ctx->partial_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes;
+    if (scratch_bytes) *scratch_bytes = ctx->tile_flags_bytes + ctx->partial_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes;
     return NB_OK;
 }
 

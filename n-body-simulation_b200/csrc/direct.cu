@@ -29,11 +29,15 @@ constexpr int STAGES = 3;
 constexpr int REC_BYTES = 16;
 constexpr int SMEM_BYTES = STAGES * TILE * REC_BYTES + 2 * STAGES * 8;
 
-template <int DIM, int PAIRS>
+// UNIFORM: every source of the tile has the reference mass, the factor m_j is hoisted out of the sum (applied once
+// in the epilogue) and an interaction costs 11 instead of 12 FP32-pipe operations.  `mscale` is 1 in the exact
+// kernels and 1/m_ref in the hoisting kernels (sources of mixed tiles then carry m_j/m_ref).
+template <int DIM, int PAIRS, bool UNIFORM>
 __device__ __forceinline__ void interact(const float4 s, const uint64_t (&BX)[PAIRS], const uint64_t (&BY)[PAIRS],
                                          const uint64_t (&BZ)[PAIRS], uint64_t (&AX)[PAIRS], uint64_t (&AY)[PAIRS],
-                                         uint64_t (&AZ)[PAIRS], const uint64_t E2) {
-    const uint64_t sx = pk2(s.x, s.x), sy = pk2(s.y, s.y), sz = pk2(s.z, s.z), sm = pk2(s.w, s.w);
+                                         uint64_t (&AZ)[PAIRS], const uint64_t E2, const float mscale, const bool scaled) {
+    const float mw = scaled ? s.w * mscale : s.w;
+    const uint64_t sx = pk2(s.x, s.x), sy = pk2(s.y, s.y), sz = pk2(s.z, s.z), sm = pk2(mw, mw);
 #pragma unroll
     for (int p = 0; p < PAIRS; p++) {
         uint64_t dx = sub2(sx, BX[p]);
@@ -50,19 +54,23 @@ __device__ __forceinline__ void interact(const float4 s, const uint64_t (&BX)[PA
         uint64_t inv = pk2(rsqrt_approx(r0), rsqrt_approx(r1));
         uint64_t sc = mul2(inv, inv);
         if (DIM == 3) sc = mul2(sc, inv);
-        sc = mul2(sc, sm);
+        if (!UNIFORM) sc = mul2(sc, sm);
         AX[p] = fma2(dx, sc, AX[p]);
         AY[p] = fma2(dy, sc, AY[p]);
         if (DIM == 3) AZ[p] = fma2(dz, sc, AZ[p]);
     }
 }
 
-template <int DIM, int PAIRS, int MINB>
+template <int DIM, int PAIRS, int MINB, bool HOIST>
 __global__ void __launch_bounds__(NT, MINB)
 direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and targets are read from here too
               int n, int target_begin, int target_count, float eps,
               float4* __restrict__ out,           // acc (jsplit == 1) or partial sums [jsplit][target_count]
-              int jsplit) {
+              int jsplit,
+              const unsigned char* __restrict__ tile_uniform,   // HOIST: 1 where all 1024 masses of a tile equal m_ref
+              const float* __restrict__ mref) {                 // HOIST: [0] = m_ref, [1] = 1/m_ref
+    float m_ref = 1.f, inv_mref = 1.f;
+    if (HOIST) { m_ref = mref[0]; inv_mref = mref[1]; }
     extern __shared__ __align__(128) unsigned char smem[];
     const float4* tiles = reinterpret_cast<const float4*>(smem);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * TILE * REC_BYTES);
@@ -117,11 +125,14 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
         mbar_wait(&full[s], (it / STAGES) & 1);
         const float4* tp = tiles + s * TILE;
         const int cnt = tile_count(tile0 + it);
-        if (cnt == TILE) {
+        if (HOIST && cnt == TILE && tile_uniform[tile0 + it]) {
 #pragma unroll 4
-            for (int j = 0; j < TILE; j++) interact<DIM, PAIRS>(tp[j], BX, BY, BZ, AX, AY, AZ, E2);
+            for (int j = 0; j < TILE; j++) interact<DIM, PAIRS, true>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, 1.f, false);
+        } else if (cnt == TILE) {
+#pragma unroll 4
+            for (int j = 0; j < TILE; j++) interact<DIM, PAIRS, false>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, inv_mref, HOIST);
         } else {  // ragged last tile of the source array
-            for (int j = 0; j < cnt; j++) interact<DIM, PAIRS>(tp[j], BX, BY, BZ, AX, AY, AZ, E2);
+            for (int j = 0; j < cnt; j++) interact<DIM, PAIRS, false>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, inv_mref, HOIST);
         }
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
@@ -144,6 +155,7 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
         up2(AX[p], x0, x1);
         up2(AY[p], y0, y1);
         if (DIM == 3) up2(AZ[p], z0, z1);
+        if (HOIST) { x0 *= m_ref; x1 *= m_ref; y0 *= m_ref; y1 *= m_ref; z0 *= m_ref; z1 *= m_ref; }
         int i0 = base + (2 * p) * NT + tid;
         int i1 = base + (2 * p + 1) * NT + tid;
         if (i0 < target_count) dst[i0] = make_float4(x0, y0, z0, 0.f);
@@ -172,7 +184,25 @@ __global__ void zero_acc_kernel(float4* acc, int n) {
     if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int);
+// Per source tile: are all masses equal to the reference mass (the mass of body n/2)?  m_ref <= 0 or non-finite
+// disables hoisting (no tile is marked).
+__global__ void __launch_bounds__(256) classify_tiles_kernel(const float4* __restrict__ pos, int n,
+                                                            unsigned char* __restrict__ tile_uniform,
+                                                            float* __restrict__ mref) {
+    const float m = pos[n / 2].w;
+    const bool usable = m > 0.f && m < 3.0e38f;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        mref[0] = usable ? m : 1.f;
+        mref[1] = usable ? 1.f / m : 1.f;
+    }
+    const int base = blockIdx.x * TILE;
+    int same = 1;
+    for (int j = threadIdx.x; j < TILE; j += blockDim.x) same &= (base + j < n && pos[base + j].w == m) ? 1 : 0;
+    same = __syncthreads_and(same);
+    if (threadIdx.x == 0) tile_uniform[blockIdx.x] = (usable && same) ? 1 : 0;
+}
+
+using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int, const unsigned char*, const float*);
 
 struct Variant {
     kernel_fn fn;
@@ -180,9 +210,11 @@ struct Variant {
     int occupancy;  // resident CTAs per SM, filled lazily
 };
 
-Variant g_variants[2][2] = {
-    {{direct_kernel<2, 2, 3>, 2, 0}, {direct_kernel<2, 4, 2>, 4, 0}},
-    {{direct_kernel<3, 2, 3>, 2, 0}, {direct_kernel<3, 4, 2>, 4, 0}},
+Variant g_variants[2][2][2] = {   // [hoist][dim - 2][pairs == 4]
+    {{{direct_kernel<2, 2, 3, false>, 2, 0}, {direct_kernel<2, 4, 2, false>, 4, 0}},
+     {{direct_kernel<3, 2, 3, false>, 2, 0}, {direct_kernel<3, 4, 2, false>, 4, 0}}},
+    {{{direct_kernel<2, 2, 3, true>, 2, 0}, {direct_kernel<2, 4, 2, true>, 4, 0}},
+     {{direct_kernel<3, 2, 3, true>, 2, 0}, {direct_kernel<3, 4, 2, true>, 4, 0}}},
 };
 
 int env_int(const char* name, int dflt) {
@@ -209,7 +241,10 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     // them, else 4 (finer granularity); NB_DIRECT_PAIRS overrides for tuning.
     int pairs = env_int("NB_DIRECT_PAIRS", 0);
     if (pairs != 2 && pairs != 4) pairs = (target_count >= ctx->sm_count * 2 * NT * 8) ? 4 : 2;
-    Variant& v = g_variants[dim - 2][pairs == 4 ? 1 : 0];
+    // Hoisting the common mass out of the sum changes the rounding (not the order) of the sum: exact mode keeps
+    // the reference arithmetic; NB_DIRECT_NO_HOIST switches it off for tuning.
+    const bool hoist = !(flags & NB_DIRECT_ORDERED) && env_int("NB_DIRECT_NO_HOIST", 0) == 0;
+    Variant& v = g_variants[hoist ? 1 : 0][dim - 2][pairs == 4 ? 1 : 0];
     if (v.occupancy == 0) {
         NB_CUDA(ctx, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         int occ = 0;
@@ -252,14 +287,24 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
         out = reinterpret_cast<float4*>(ctx->partial);
     }
 
+    int launches = 1;
+    unsigned char* flags_d = nullptr;
+    float* mref_d = nullptr;
+    if (hoist) {
+        rc = nb_reserve(ctx, &ctx->tile_flags, &ctx->tile_flags_bytes, (size_t)ntiles + 64);
+        if (rc) return rc;
+        mref_d = reinterpret_cast<float*>(ctx->tile_flags);
+        flags_d = reinterpret_cast<unsigned char*>(ctx->tile_flags) + 64;
+        classify_tiles_kernel<<<ntiles, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, flags_d, mref_d);
+        launches++;
+    }
     dim3 grid(tblocks, jsplit);
     v.fn<<<grid, NT, SMEM_BYTES, stream>>>(reinterpret_cast<const float4*>(pos), n, target_begin, target_count,
-                                           softening, out, jsplit);
-    int launches = 1;
+                                           softening, out, jsplit, flags_d, mref_d);
     if (jsplit > 1) {
         reduce_partials_kernel<<<(target_count + 255) / 256, 256, 0, stream>>>(
             reinterpret_cast<const float4*>(ctx->partial), target_count, jsplit, reinterpret_cast<float4*>(acc));
-        launches = 2;
+        launches++;
     }
     NB_CUDA(ctx, cudaGetLastError());
     ctx->last_jsplit = jsplit;
@@ -324,7 +369,7 @@ extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int 
     if (e != cudaSuccess) return noalloc_fail(NB_ERR_NO_DEVICE, "nb_direct_accel_noalloc: cudaGetDevice", e);
     if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: device index");
     NoAllocDevice& d = g_noalloc_dev[dev];
-    kernel_fn fn = dim == 2 ? (kernel_fn)direct_kernel<2, 2, 3> : (kernel_fn)direct_kernel<3, 2, 3>;
+    kernel_fn fn = dim == 2 ? (kernel_fn)direct_kernel<2, 2, 3, false> : (kernel_fn)direct_kernel<3, 2, 3, false>;
     {
         std::lock_guard<std::mutex> lock(g_noalloc_mutex);
         if (!d.ready) {
@@ -335,7 +380,7 @@ extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int 
             if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaGetSymbolAddress", e);
             e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev);
             if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaDeviceGetAttribute", e);
-            kernel_fn fns[2] = {(kernel_fn)direct_kernel<2, 2, 3>, (kernel_fn)direct_kernel<3, 2, 3>};
+            kernel_fn fns[2] = {(kernel_fn)direct_kernel<2, 2, 3, false>, (kernel_fn)direct_kernel<3, 2, 3, false>};
             for (int k = 0; k < 2; k++) {
                 e = cudaFuncSetAttribute(fns[k], cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
                 if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaFuncSetAttribute", e);
@@ -373,7 +418,8 @@ extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int 
 
     cudaStream_t s = (cudaStream_t)stream;
     float4* out = jsplit > 1 ? d.scratch : reinterpret_cast<float4*>(acc);
-    fn<<<dim3(tblocks, jsplit), NT, SMEM_BYTES, s>>>(reinterpret_cast<const float4*>(pos), n, 0, n, softening, out, jsplit);
+    fn<<<dim3(tblocks, jsplit), NT, SMEM_BYTES, s>>>(reinterpret_cast<const float4*>(pos), n, 0, n, softening, out, jsplit,
+                                                     nullptr, nullptr);
     if (jsplit > 1)
         reduce_partials_kernel<<<(n + 255) / 256, 256, 0, s>>>(d.scratch, n, jsplit, reinterpret_cast<float4*>(acc));
     e = cudaGetLastError();
