@@ -691,6 +691,173 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// walk, list-building form.  Same accepted set as walk_kernel (and as the reference), different schedule:
+// the 32 lanes of a group classify 32 DIFFERENT child records at a time instead of all testing the same one.
+//   * a cell fails the unanimous vote as soon as ONE target fails it: every lane tests its record against the
+//     group's first target with the reference's own arithmetic -> "rejected" is exact;
+//   * a cell certainly passes if thr <= (eps + squared distance to the group's bounding box) with a 1e-6 safety
+//     margin for FP32 rounding -> "accepted" is exact;
+//   * whatever falls between the two is decided by the real 32-lane vote (src/BarnesHutKernels.cu:430).
+// Accepted records go to a shared-memory list that all lanes then evaluate for their own target (k = m / r,
+// :431-433); rejected nodes go to a LIFO of node ids that is popped eight nodes (32 child records) at a time.
+// Summation order differs from the depth-first walk (FP32 rounding only).
+// ------------------------------------------------------------------------------------------------------
+constexpr int WL_WARPS = 4;
+constexpr int WL_QCAP = 2048;   // node ids per group
+constexpr int WL_LCAP = 64;     // pending accepted records per group
+
+template <bool COUNT>
+__global__ void __launch_bounds__(WL_WARPS * 32) walk_lists_kernel(const float4* __restrict__ pos,
+                                                                  const int32_t* __restrict__ sorted_idx, int n,
+                                                                  const float4* __restrict__ cblk,
+                                                                  const uint32_t* __restrict__ clink,   // 4 links per node
+                                                                  const float4* __restrict__ spos,
+                                                                  const float4* __restrict__ root_rec, float eps,
+                                                                  int group_begin, int group_count, float4* __restrict__ acc,
+                                                                  unsigned long long* __restrict__ counters) {
+    __shared__ uint32_t q_s[WL_WARPS][WL_QCAP];
+    __shared__ float4 l_s[WL_WARPS][WL_LCAP];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned FULLM = 0xffffffffu;
+    const int g = blockIdx.x * WL_WARPS + warp;
+    if (g >= group_count) return;
+    const int bi = (group_begin + g) * 32 + lane;
+    const bool valid = bi < n;
+    // lanes past the end of the sorted order shadow the group's first target: they vote like it and store nothing
+    const int body = sorted_idx[valid ? bi : (group_begin + g) * 32];
+    const float4 me = pos[body];
+    const float x = me.x, y = me.y;
+    const float xr = __shfl_sync(FULLM, x, 0), yr = __shfl_sync(FULLM, y, 0);
+    float bx0 = x, bx1 = x, by0 = y, by1 = y;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        bx0 = fminf(bx0, __shfl_xor_sync(FULLM, bx0, o));
+        bx1 = fmaxf(bx1, __shfl_xor_sync(FULLM, bx1, o));
+        by0 = fminf(by0, __shfl_xor_sync(FULLM, by0, o));
+        by1 = fmaxf(by1, __shfl_xor_sync(FULLM, by1, o));
+    }
+    float ax = 0.f, ay = 0.f;
+    uint32_t* const q = q_s[warp];
+    float4* const lst = l_s[warp];
+    int qtop = 0, lcount = 0;
+    unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
+    int c_depth = 0;
+    bool overflow = false;
+
+    auto add = [&](float cx, float cy, float m) {
+        const float dx = cx - x, dy = cy - y;
+        const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+        const float k = rcp_approx(r) * m;
+        ax = __fmaf_rn(k, dx, ax);
+        ay = __fmaf_rn(k, dy, ay);
+    };
+    auto flush = [&]() {
+        __syncwarp();
+        for (int k = 0; k < lcount; k++) {
+            const float4 c = lst[k];
+            add(c.x, c.y, c.z);
+        }
+        __syncwarp();
+        lcount = 0;
+    };
+
+    // the lane's current record; lane 0 starts with the root cell itself
+    float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t link = LINK_EMPTY;
+    if (lane == 0) {
+        rec = root_rec[0];
+        link = __float_as_uint(root_rec[1].x);
+    }
+    for (;;) {
+        // ---- classify this lane's record ---------------------------------------------------------------
+        const bool present = link != LINK_EMPTY;
+        bool rej = false, amb = false, accp = false;
+        if (present) {
+            const float dxr = rec.x - xr, dyr = rec.y - yr;
+            const float rr = __fmaf_rn(dyr, dyr, __fmaf_rn(dxr, dxr, eps));     // the first target's own vote
+            if (!(rec.w <= rr)) {
+                rej = true;
+            } else {
+                const float ddx = fmaxf(fmaxf(bx0 - rec.x, rec.x - bx1), 0.f);
+                const float ddy = fmaxf(fmaxf(by0 - rec.y, rec.y - by1), 0.f);
+                const float dmin = __fmaf_rn(ddy, ddy, __fmaf_rn(ddx, ddx, eps));
+                if (rec.w <= dmin * 0.999999f) accp = true; else amb = true;
+            }
+        }
+        // ---- undecided records: the real unanimous vote --------------------------------------------------
+        unsigned ambm = __ballot_sync(FULLM, amb);
+        while (ambm) {
+            const int src = __ffs(ambm) - 1;
+            ambm &= ambm - 1;
+            const float cx = __shfl_sync(FULLM, rec.x, src), cy = __shfl_sync(FULLM, rec.y, src);
+            const float cm = __shfl_sync(FULLM, rec.z, src), ct = __shfl_sync(FULLM, rec.w, src);
+            const float dx = cx - x, dy = cy - y;
+            const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+            if (__all_sync(FULLM, ct <= r)) {
+                const float k = rcp_approx(r) * cm;
+                ax = __fmaf_rn(k, dx, ax);
+                ay = __fmaf_rn(k, dy, ay);
+                if (COUNT) c_inter++;
+            } else if (lane == src) {
+                rej = true;
+            }
+        }
+        // ---- accepted -> interaction list, rejected -> node LIFO -----------------------------------------
+        const unsigned accm = __ballot_sync(FULLM, accp);
+        const unsigned rejm = __ballot_sync(FULLM, rej);
+        const unsigned below = (1u << lane) - 1u;
+        if (COUNT) { c_exam += __popc(__ballot_sync(FULLM, present)); c_inter += __popc(accm); }
+        if (accp) lst[lcount + __popc(accm & below)] = rec;
+        lcount += __popc(accm);
+        if (lcount >= 32) flush();
+        const int nrej = __popc(rejm);
+        if (qtop + nrej > WL_QCAP) { overflow = true; break; }
+        if (rej) q[qtop + __popc(rejm & below)] = link;
+        qtop += nrej;
+        __syncwarp();
+        if (COUNT) c_depth = max(c_depth, qtop);
+        if (qtop == 0) break;
+        // ---- pop up to eight nodes: lane l takes child (l & 3) of the (l >> 2)-th node from the top ----------
+        const int k = min(8, qtop);
+        const int slot = lane >> 2;
+        uint32_t ent = LINK_EMPTY;
+        if (slot < k) ent = q[qtop - 1 - slot];
+        __syncwarp();
+        qtop -= k;
+        if (COUNT) c_open += k;
+        link = LINK_EMPTY;
+        const bool is_bucket = (ent != LINK_EMPTY) && (ent & LINK_BUCKET);
+        if (ent != LINK_EMPTY && !is_bucket) {
+            const uint32_t id = ent & 0x7FFFFFFFu;
+            rec = cblk[4 * (size_t)id + (lane & 3)];
+            link = clink[4 * (size_t)id + (lane & 3)];
+        }
+        unsigned bm = __ballot_sync(FULLM, is_bucket && (lane & 3) == 0);
+        while (bm) {   // depth-cap buckets: every body of the cell, summed by all lanes
+            const int src = __ffs(bm) - 1;
+            bm &= bm - 1;
+            const uint32_t id = __shfl_sync(FULLM, ent, src) & 0x7FFFFFFFu;
+            const float4 h = cblk[4 * (size_t)id];
+            const int first = __float_as_int(h.x), cnt = __float_as_int(h.y);
+            for (int t = 0; t < cnt; t++) {
+                const float4 p = spos[first + t];
+                add(p.x, p.y, p.z);
+            }
+            if (COUNT) { c_exam += cnt; c_inter += cnt; }
+        }
+    }
+    flush();
+    if (valid) acc[body] = make_float4(ax, ay, 0.f, 0.f);
+    if (overflow && lane == 0) atomicOr(&counters[4], 1ull);
+    if (COUNT && lane == 0) {
+        atomicAdd(&counters[0], c_open);
+        atomicAdd(&counters[1], c_exam);
+        atomicMax(&counters[3], (unsigned long long)c_depth);
+    }
+    if (COUNT && valid) atomicAdd(&counters[2], c_inter);   // lane interactions: per valid target
+}
+
 __global__ void zero_acc_kernel(float4* acc, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -818,14 +985,25 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
         zero_acc_kernel<<<1, 32, 0, stream>>>(acc, 1);
         return NB_OK;
     }
-    const int blocks = (group_count + WALK_WARPS - 1) / WALK_WARPS;
-    if (count) {
-        cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
-        walk_kernel<true><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
-                                                                 st->root_rec, eps, group_begin, group_count, acc, st->counters);
+    static const int use_dfs = [] { const char* v = getenv("NB_BH_WALK"); return (v && v[0] == 'd') ? 1 : 0; }();
+    if (count) cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
+    if (use_dfs) {   // depth-first walk in the reference's own order (kept for comparison: NB_BH_WALK=dfs)
+        const int blocks = (group_count + WALK_WARPS - 1) / WALK_WARPS;
+        if (count)
+            walk_kernel<true><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
+                                                                     st->root_rec, eps, group_begin, group_count, acc, st->counters);
+        else
+            walk_kernel<false><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
+                                                                      st->root_rec, eps, group_begin, group_count, acc, st->counters);
     } else {
-        walk_kernel<false><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
-                                                                  st->root_rec, eps, group_begin, group_count, acc, st->counters);
+        const int blocks = (group_count + WL_WARPS - 1) / WL_WARPS;
+        const uint32_t* links = reinterpret_cast<const uint32_t*>(st->clink);
+        if (count)
+            walk_lists_kernel<true><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, st->spos,
+                                                                         st->root_rec, eps, group_begin, group_count, acc, st->counters);
+        else
+            walk_lists_kernel<false><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, st->spos,
+                                                                          st->root_rec, eps, group_begin, group_count, acc, st->counters);
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
