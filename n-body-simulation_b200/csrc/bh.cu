@@ -51,9 +51,10 @@ struct nb_bh_state {
     int32_t* idx32[2] = {nullptr, nullptr};
     uint64_t* key64[2] = {nullptr, nullptr};
     int32_t* idx64[2] = {nullptr, nullptr};
-    uint32_t* hist = nullptr;          // radix histograms [256][blocks]
-    size_t hist_elems = 0;
-    uint32_t* digit_total = nullptr;   // [256]
+    uint32_t* ghist = nullptr;         // [12][256] global digit histograms, then 12 tile tickets, then the status words
+    uint32_t* os_status = nullptr;     // [12][os_stride] look-back status, os_stride = tiles * 256
+    unsigned int* os_ticket = nullptr; // [12]
+    size_t os_stride = 0, os_bytes = 0;
     float4* spos = nullptr;            // bodies in tree order: (x, y, m, -)
     D3* psum = nullptr;                // chunk-local inclusive prefix sums of (m, m x, m y)
     D3* psum_blk = nullptr;            // exclusive prefix of the chunk totals
@@ -144,117 +145,99 @@ __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* par
 // keys: SFC key (src/BarnesHutKernels.cu:197-240, strict '>') and 64-bit tree-path key (the '>=' descent of
 // :266-285, digit = path ^ 2 so that both orders agree away from exact midpoint hits)
 // ------------------------------------------------------------------------------------------------------
-__global__ void keys_kernel(const float4* __restrict__ pos, int n, const float4* __restrict__ bounds,
-                            uint32_t* __restrict__ key32, int32_t* __restrict__ idx32,
-                            uint64_t* __restrict__ key64, int32_t* __restrict__ idx64) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+constexpr int KEYS_THREADS = 256;
+constexpr int KEYS_PER_BLOCK = 4096;
+constexpr int N_DIGITS = 12;   // 4 digits of the 32-bit SFC key, then 8 digits of the 64-bit tree key
+
+__global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __restrict__ pos, int n,
+                                                           const float4* __restrict__ bounds,
+                                                           uint32_t* __restrict__ key32, uint64_t* __restrict__ key64,
+                                                           uint32_t* __restrict__ ghist /* [12][256] or null */) {
+    __shared__ uint32_t h[N_DIGITS][256];
+    if (ghist) {
+        for (int k = threadIdx.x; k < N_DIGITS * 256; k += KEYS_THREADS) (&h[0][0])[k] = 0;
+        __syncthreads();
+    }
     const float4 bb = *bounds;
-    const float4 p = pos[i];
-    {
-        float l = bb.x, r = bb.z, b = bb.y, t = bb.w;
-        uint32_t key = 0;
+    for (int i = blockIdx.x * KEYS_PER_BLOCK + threadIdx.x; i < min(n, (blockIdx.x + 1) * KEYS_PER_BLOCK); i += KEYS_THREADS) {
+        const float4 p = pos[i];
+        uint32_t k32 = 0;
+        {
+            float l = bb.x, r = bb.z, b = bb.y, t = bb.w;
 #pragma unroll
-        for (int s = 30; s >= 0; s -= 2) {
-            const float midX = (r + l) * 0.5f;
-            const float midY = (t + b) * 0.5f;
-            if (p.x > midX) {
-                l = midX;
-                if (p.y > midY) { b = midY; key |= 1u << s; }
-                else            { t = midY; key |= 3u << s; }
-            } else {
-                r = midX;
-                if (p.y > midY) { b = midY; }
-                else            { t = midY; key |= 2u << s; }
+            for (int s = 30; s >= 0; s -= 2) {
+                const float midX = (r + l) * 0.5f;
+                const float midY = (t + b) * 0.5f;
+                if (p.x > midX) {
+                    l = midX;
+                    if (p.y > midY) { b = midY; k32 |= 1u << s; }
+                    else            { t = midY; k32 |= 3u << s; }
+                } else {
+                    r = midX;
+                    if (p.y > midY) { b = midY; }
+                    else            { t = midY; k32 |= 2u << s; }
+                }
             }
         }
-        key32[i] = key;
-        idx32[i] = i;
-    }
-    {
-        float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
-        uint64_t key = 0;
+        uint64_t k64 = 0;
+        {
+            float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
 #pragma unroll 8
-        for (int lev = 0; lev < MAX_LEVEL; lev++) {
-            unsigned path = 0;
-            const float midX = (maxX + minX) * 0.5f;
-            if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
-            const float midY = (maxY + minY) * 0.5f;
-            if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
-            key |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
+            for (int lev = 0; lev < MAX_LEVEL; lev++) {
+                unsigned path = 0;
+                const float midX = (maxX + minX) * 0.5f;
+                if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
+                const float midY = (maxY + minY) * 0.5f;
+                if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
+                k64 |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
+            }
         }
-        key64[i] = key;
-        idx64[i] = i;
+        key32[i] = k32;
+        key64[i] = k64;
+        if (ghist) {
+#pragma unroll
+            for (int d = 0; d < 4; d++) atomicAdd(&h[d][(k32 >> (8 * d)) & 255u], 1u);
+#pragma unroll
+            for (int d = 0; d < 8; d++) atomicAdd(&h[4 + d][(uint32_t)(k64 >> (8 * d)) & 255u], 1u);
+        }
+    }
+    if (ghist) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < N_DIGITS * 256; k += KEYS_THREADS) {
+            const uint32_t v = (&h[0][0])[k];
+            if (v) atomicAdd(&ghist[k], v);
+        }
     }
 }
 
 // ------------------------------------------------------------------------------------------------------
-// stable LSD radix sort, 8-bit digits (replaces thrust::sort_by_key, src/BarnesHutKernels.cu:45)
+// stable LSD radix sort, 8-bit digits, one kernel per digit (replaces thrust::sort_by_key,
+// src/BarnesHutKernels.cu:45).  The global digit histograms come from keys_kernel; each pass ranks its tile
+// with warp-level match.any (stable), and tiles chain their per-digit prefixes through a status word per
+// (tile, digit) -- count << 2 | {1: tile total, 2: inclusive prefix} -- read backwards until an inclusive
+// prefix is met ("decoupled look-back").  Tile numbers are handed out by an atomic ticket, so a tile only
+// ever waits on tiles that already started.
 // ------------------------------------------------------------------------------------------------------
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 keys per block
 
 template <typename K>
-__global__ void __launch_bounds__(SORT_THREADS) sort_hist_kernel(const K* __restrict__ keys, int n, int shift,
-                                                                uint32_t* __restrict__ hist, int nblocks) {
-    __shared__ uint32_t h[256];
-    h[threadIdx.x] = 0;
-    __syncthreads();
-    const int base = blockIdx.x * SORT_TILE;
-#pragma unroll
-    for (int k = 0; k < SORT_ITEMS; k++) {
-        const int i = base + k * SORT_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&h[(uint32_t)(keys[i] >> shift) & 255u], 1u);
-    }
-    __syncthreads();
-    hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];  // digit-major
-}
-
-// Block d turns row d of the digit-major histogram (one count per sort tile) into an exclusive prefix over
-// the tiles and stores the row total; the digit bases are added by the scatter kernel.
-__global__ void __launch_bounds__(256) scan_rows_kernel(uint32_t* __restrict__ hist, int nblocks,
-                                                       uint32_t* __restrict__ digit_total) {
-    __shared__ uint32_t wsum[8];
-    uint32_t* row = hist + (size_t)blockIdx.x * nblocks;
-    const int per = (nblocks + 255) / 256;
-    const int i0 = threadIdx.x * per;
-    uint32_t s = 0;
-    for (int k = 0; k < per; k++) s += (i0 + k < nblocks) ? row[i0 + k] : 0u;
-    uint32_t inc = s;
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if ((threadIdx.x & 31) >= o) inc += t;
-    }
-    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
-    __syncthreads();
-    uint32_t run = inc - s;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) run += wsum[w];
-    for (int k = 0; k < per; k++) {
-        if (i0 + k < nblocks) {
-            const uint32_t v = row[i0 + k];
-            row[i0 + k] = run;
-            run += v;
-        }
-    }
-    if (threadIdx.x == 255) digit_total[blockIdx.x] = run;
-}
-
-template <typename K>
-__global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __restrict__ keys_in,
-                                                                   const int32_t* __restrict__ vals_in, int n, int shift,
-                                                                   const uint32_t* __restrict__ offs, int nblocks,
-                                                                   const uint32_t* __restrict__ digit_total,
-                                                                   K* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
-    // tile order = warp-major, round-major, lane: warp w owns keys [w*512, (w+1)*512) of the tile
+__global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restrict__ keys_in,
+                                                               const int32_t* __restrict__ vals_in,   // null: identity
+                                                               int n, int shift, const uint32_t* __restrict__ ghist,
+                                                               uint32_t* status, unsigned int* ticket,
+                                                               K* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
     constexpr int WARPS = SORT_THREADS / 32;
     __shared__ uint32_t cnt[WARPS][256];
     __shared__ uint32_t dbase[256];
     __shared__ uint32_t dw[WARPS];
+    __shared__ unsigned int tile_s;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) tile_s = atomicAdd(ticket, 1u);
     for (int d = lane; d < 256; d += 32) cnt[warp][d] = 0;
-    {   // exclusive prefix of the 256 digit totals = where each digit's bin starts in the output
-        const uint32_t v = digit_total[threadIdx.x];
+    {   // exclusive prefix of the 256 global digit counts = where each digit's bin starts in the output
+        const uint32_t v = ghist[threadIdx.x];
         uint32_t inc = v;
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -266,15 +249,20 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __r
         for (int w = 0; w < warp; w++) off += dw[w];
         dbase[threadIdx.x] = off;
     }
-    __syncwarp();
-    const int wbase = blockIdx.x * SORT_TILE + warp * (32 * SORT_ITEMS);
+    const int tile = (int)tile_s;
+    // tile order = warp-major, round-major, lane: warp w owns keys [w*512, (w+1)*512) of the tile
+    const int wbase = tile * SORT_TILE + warp * (32 * SORT_ITEMS);
     K key[SORT_ITEMS];
     uint32_t rank[SORT_ITEMS];
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
         const int i = wbase + k * 32 + lane;
+        key[k] = i < n ? keys_in[i] : (K)0;
+    }
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int i = wbase + k * 32 + lane;
         const bool valid = i < n;
-        key[k] = valid ? keys_in[i] : (K)0;
         rank[k] = 0;
         const unsigned act = __ballot_sync(0xffffffffu, valid);
         if (valid) {
@@ -292,15 +280,26 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __r
         __syncwarp();
     }
     __syncthreads();
-    {   // per digit: exclusive prefix over warps, plus the global offset of this block's digit bin
+    {   // per digit: exclusive prefix over the warps of this tile, then over the tiles before it
         const int d = threadIdx.x;
-        uint32_t run = dbase[d] + offs[(size_t)d * nblocks + blockIdx.x];
+        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < WARPS; w++) {
             const uint32_t c = cnt[w][d];
             cnt[w][d] = run;
             run += c;
         }
+        volatile uint32_t* st = status;
+        st[(size_t)tile * 256 + d] = (run << 2) | (tile == 0 ? 2u : 1u);
+        uint32_t excl = 0;
+        for (int p = tile - 1; p >= 0; --p) {
+            uint32_t v;
+            do { v = st[(size_t)p * 256 + d]; } while ((v & 3u) == 0u);
+            excl += v >> 2;
+            if ((v & 3u) == 2u) break;
+        }
+        if (tile > 0) st[(size_t)tile * 256 + d] = ((excl + run) << 2) | 2u;
+        dbase[d] += excl;
     }
     __syncthreads();
 #pragma unroll
@@ -308,23 +307,23 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const K* __r
         const int i = wbase + k * 32 + lane;
         if (i < n) {
             const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
-            const uint32_t dst = cnt[warp][d] + rank[k];
+            const uint32_t dst = dbase[d] + cnt[warp][d] + rank[k];
             keys_out[dst] = key[k];
-            vals_out[dst] = vals_in[i];
+            vals_out[dst] = vals_in ? vals_in[i] : i;
         }
     }
 }
 
+// `digit0`: index of this sort's first digit in the [12][256] histogram / status layout.
 template <typename K>
-int radix_sort(nb_context* ctx, nb_bh_state* st, K* keys[2], int32_t* vals[2], int n, int bits, int* sel_out,
+int radix_sort(nb_context* ctx, nb_bh_state* st, K* keys[2], int32_t* vals[2], int n, int bits, int digit0, int* sel_out,
                cudaStream_t stream) {
     const int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
     int sel = 0;
-    for (int shift = 0; shift < bits; shift += 8) {
-        sort_hist_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], n, shift, st->hist, nblocks);
-        scan_rows_kernel<<<256, 256, 0, stream>>>(st->hist, nblocks, st->digit_total);
-        sort_scatter_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], vals[sel], n, shift, st->hist, nblocks,
-                                                                    st->digit_total, keys[sel ^ 1], vals[sel ^ 1]);
+    for (int shift = 0, d = digit0; shift < bits; shift += 8, d++) {
+        onesweep_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], shift == 0 ? nullptr : vals[sel], n, shift,
+                                                                st->ghist + 256 * d, st->os_status + (size_t)d * st->os_stride,
+                                                                st->os_ticket + d, keys[sel ^ 1], vals[sel ^ 1]);
         sel ^= 1;
     }
     *sel_out = sel;
@@ -704,11 +703,11 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
 // Summation order differs from the depth-first walk (FP32 rounding only).
 // ------------------------------------------------------------------------------------------------------
 constexpr int WL_WARPS = 4;
-constexpr int WL_QCAP = 2048;   // node ids per group
+constexpr int WL_QCAP = 1024;   // node ids per group (measured peak at N = 1M, theta = 0.5: see bench counters)
 constexpr int WL_LCAP = 64;     // pending accepted records per group
 
 template <bool COUNT>
-__global__ void __launch_bounds__(WL_WARPS * 32) walk_lists_kernel(const float4* __restrict__ pos,
+__global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const float4* __restrict__ pos,
                                                                   const int32_t* __restrict__ sorted_idx, int n,
                                                                   const float4* __restrict__ cblk,
                                                                   const uint32_t* __restrict__ clink,   // 4 links per node
@@ -754,6 +753,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32) walk_lists_kernel(const float4*
     };
     auto flush = [&]() {
         __syncwarp();
+#pragma unroll 4
         for (int k = 0; k < lcount; k++) {
             const float4 c = lst[k];
             add(c.x, c.y, c.z);
@@ -872,7 +872,7 @@ int alloc(nb_context* ctx, T** p, size_t count) {
 void free_state(nb_bh_state* st) {
     if (!st) return;
     void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
-                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->hist, st->digit_total, st->clink, st->spos, st->psum, st->psum_blk,
+                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->ghist, st->clink, st->spos, st->psum, st->psum_blk,
                     st->left, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
                     st->node_top, st->root, st->root_rec, st->counters};
     for (void* p : ptrs)
@@ -908,9 +908,11 @@ int ensure_state(nb_context* ctx, int n) {
         rc |= alloc(ctx, &st->key64[k], cap);
         rc |= alloc(ctx, &st->idx64[k], cap);
     }
-    st->hist_elems = 256 * sblocks;
-    rc |= alloc(ctx, &st->hist, st->hist_elems);
-    rc |= alloc(ctx, &st->digit_total, 256);
+    const size_t os_words = (size_t)N_DIGITS * 256 + 64 + (size_t)N_DIGITS * 256 * sblocks;
+    st->os_bytes = os_words * sizeof(uint32_t);
+    rc |= alloc(ctx, &st->ghist, os_words);
+    st->os_ticket = reinterpret_cast<unsigned int*>(st->ghist + N_DIGITS * 256);
+    st->os_status = st->ghist + N_DIGITS * 256 + 64;
     rc |= alloc(ctx, &st->spos, cap);
     rc |= alloc(ctx, &st->psum, cap);
     rc |= alloc(ctx, &st->psum_blk, chunks);
@@ -948,13 +950,19 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
     int bblocks = std::min(1024, std::max(1, (n + 1023) / 1024));
     bounds_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, accumulate);
     st->bounds_valid = true;
-    if (upto >= 2)
-        keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(pos, n, st->bounds, st->key32[0], st->idx32[0], st->key64[0],
-                                                         st->idx64[0]);
+    if (upto >= 2) {
+        // one memset clears the digit histograms, the tile tickets and the look-back status words of all 12 passes
+        const int tiles = (n + SORT_TILE - 1) / SORT_TILE;
+        st->os_stride = (size_t)tiles * 256;   // compact for this n, so that the words to clear are contiguous
+        NB_CUDA(ctx, cudaMemsetAsync(st->ghist, 0, ((size_t)N_DIGITS * 256 + 64 + N_DIGITS * st->os_stride) * sizeof(uint32_t),
+                                     stream));
+        keys_kernel<<<(n + KEYS_PER_BLOCK - 1) / KEYS_PER_BLOCK, KEYS_THREADS, 0, stream>>>(pos, n, st->bounds, st->key32[0],
+                                                                                          st->key64[0], st->ghist);
+    }
     if (upto >= 3) {
-        rc = radix_sort<uint32_t>(ctx, st, st->key32, st->idx32, n, 32, &st->sfc_sel, stream);
+        rc = radix_sort<uint32_t>(ctx, st, st->key32, st->idx32, n, 32, 0, &st->sfc_sel, stream);
         if (rc) return rc;
-        rc = radix_sort<uint64_t>(ctx, st, st->key64, st->idx64, n, 64, &st->tree_sel, stream);
+        rc = radix_sort<uint64_t>(ctx, st, st->key64, st->idx64, n, 64, 4, &st->tree_sel, stream);
         if (rc) return rc;
     }
     if (upto >= 4 && n >= 2) {
@@ -1085,9 +1093,9 @@ int nb_bh_stages_host(nb_context* ctx, const float* pos, int n, int flags, float
     if (sorted_idx) NB_CUDA(ctx, cudaMemcpy(sorted_idx, st->idx32[st->sfc_sel], (size_t)n * 4, cudaMemcpyDeviceToHost));
     if (keys || tree_keys) {
         // keys in body order: rerun the key kernel into the scratch halves the sorts no longer need
-        keys_kernel<<<(n + 255) / 256, 256>>>(reinterpret_cast<const float4*>(pos), n, st->bounds, st->key32[st->sfc_sel ^ 1],
-                                              st->idx32[st->sfc_sel ^ 1], st->key64[st->tree_sel ^ 1],
-                                              st->idx64[st->tree_sel ^ 1]);
+        keys_kernel<<<(n + KEYS_PER_BLOCK - 1) / KEYS_PER_BLOCK, KEYS_THREADS>>>(reinterpret_cast<const float4*>(pos), n, st->bounds,
+                                                                               st->key32[st->sfc_sel ^ 1],
+                                                                               st->key64[st->tree_sel ^ 1], nullptr);
         NB_CUDA(ctx, cudaDeviceSynchronize());
         if (keys) NB_CUDA(ctx, cudaMemcpy(keys, st->key32[st->sfc_sel ^ 1], (size_t)n * 4, cudaMemcpyDeviceToHost));
         if (tree_keys) NB_CUDA(ctx, cudaMemcpy(tree_keys, st->key64[st->tree_sel ^ 1], (size_t)n * 8, cudaMemcpyDeviceToHost));
