@@ -1,0 +1,51 @@
+// dropin_main.cu -- a small driver written against the REFERENCE's own classes (NbodySystem, Verlet_DKD,
+// DiskModel, SimulationStats).  TEST INFRASTRUCTURE.  oracle/build_dropin.sh links it twice:
+//   oracle/_ref/nbody_ref_prog     with the reference's ComputeMethods.cpp + DirectComputeKernels.cu + BarnesHutKernels.cu
+//   oracle/_ref/nbody_dropin_prog  with n-body-simulation_b200/adapter/ComputeMethods.cpp + libnbody_b200.so
+// Everything else (NbodySystem.cpp, IntegrationMethods.cu, InitialConditions.cu, SimulationStats.cu, Callbacks.cpp)
+// is the reference's source in both, so the pair shows the engine dropping in behind an unchanged caller and
+// lets the energy drift of the two be compared over many steps.
+//   usage: prog <direct|bh> <n> <steps> <theta> <out.bin>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <tuple>
+
+#include "NbodySystem.h"
+
+int main(int argc, char** argv) {
+    if (argc < 6) {
+        std::printf("usage: %s <direct|bh> <n> <steps> <theta> <out.bin>\n", argv[0]);
+        return 2;
+    }
+    const bool bh = std::strcmp(argv[1], "bh") == 0;
+    const int n = std::atoi(argv[2]);
+    const int steps = std::atoi(argv[3]);
+    const float theta = (float)std::atof(argv[4]);
+    const float softening = 1.01f, dt = 0.001f;   // src/main.cu:7,12
+
+    ComputeMethods::ComputeMethod* compute =
+        bh ? (ComputeMethods::ComputeMethod*)new ComputeMethods::BarnesHut(theta, 3, softening)
+           : (ComputeMethods::ComputeMethod*)new ComputeMethods::Direct(softening);
+    auto integrator = new IntegrationMethods::Verlet_DKD();
+    NbodySystem system(n, Space::R2, compute, integrator);
+    auto ic = new InitialConditions::DiskModel({0, 0}, {0, 0}, {30000, 30000}, {70000, 70000}, {0, 0});   // src/main.cu:26-32
+    system.initSystem(0, n, ic);
+
+    auto [m0, k0, p0] = SimulationStats::computeStats(system.space, system.device.pos_mass, system.device.vel, n);
+    system.simulate(steps, dt);
+    cudaDeviceSynchronize();
+    auto [m1, k1, p1] = SimulationStats::computeStats(system.space, system.device.pos_mass, system.device.vel, n);
+    std::printf("RESULT method=%s n=%d steps=%d E0=%.12e E1=%.12e drift=%.6e moment_drift=%.6e\n", argv[1], n, steps, k0 + p0,
+                k1 + p1, (k1 + p1 - k0 - p0) / (k0 + p0), (m1 - m0) / m0);
+    system.updateHostData();
+    FILE* f = std::fopen(argv[5], "wb");
+    if (f) {
+        std::fwrite(system.host.pos_mass, sizeof(float4), n, f);
+        std::fwrite(system.host.vel, sizeof(float4), n, f);
+        std::fclose(f);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) std::printf("CUDA error: %s\n", cudaGetErrorString(e));
+    return e == cudaSuccess ? 0 : 1;
+}

@@ -1,0 +1,43 @@
+"""Drop-in proof and energy drift (BASELINE.json north_star: "Total-energy drift must track the reference over
+1000 steps").  oracle/build_dropin.sh links the reference's UNCHANGED NbodySystem / Verlet_DKD / DiskModel /
+SimulationStats once with the reference's own ComputeMethods + kernels and once with the adapter + libnbody_b200.so;
+both run the same 1000 Leapfrog steps from the reference's own initial conditions."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref", "nbody_ref_prog")
+OURS = os.path.join(ROOT, "oracle", "_ref", "nbody_dropin_prog")
+
+
+def _run(prog, method, n, steps, theta, out):
+    r = subprocess.run([prog, method, str(n), str(steps), str(theta), out], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    m = re.search(r"RESULT .*E0=(\S+) E1=(\S+) drift=(\S+) moment_drift=(\S+)", r.stdout)
+    assert m, r.stdout[-2000:]
+    state = np.fromfile(out, dtype=np.float32).reshape(2, n, 4)
+    return dict(E0=float(m.group(1)), E1=float(m.group(2)), drift=float(m.group(3)), mdrift=float(m.group(4)),
+                pos=state[0], vel=state[1])
+
+
+@pytest.mark.parametrize("method,n,theta", [("direct", 4096, 0.5), ("bh", 8192, 0.5)])
+def test_energy_drift_tracks_reference_over_1000_steps(tmp_path, method, n, theta):
+    if not (os.path.exists(REF) and os.path.exists(OURS)):
+        pytest.skip("oracle/_ref drop-in programs not built (needs /root/reference at build time)")
+    steps = 1000
+    a = _run(REF, method, n, steps, theta, str(tmp_path / "ref.bin"))
+    b = _run(OURS, method, n, steps, theta, str(tmp_path / "ours.bin"))
+    # same initial state (the reference's own generator + one force evaluation for the velocities)
+    assert abs(a["E0"] - b["E0"]) <= 1e-5 * abs(a["E0"])
+    # drift of the same size (both are tiny: symplectic integrator, dt = 0.001)
+    assert abs(b["drift"]) <= 2.0 * abs(a["drift"]) + 1e-6, (a["drift"], b["drift"])
+    assert abs(b["drift"] - a["drift"]) <= 0.5 * abs(a["drift"]) + 1e-6, (a["drift"], b["drift"])
+    # trajectories stay together: positions within 1e-4 of the disc radius after 1000 steps
+    d = np.linalg.norm(a["pos"][:, :2] - b["pos"][:, :2], axis=1)
+    assert np.quantile(d, 0.99) < 1e-4 * 30000.0, (np.median(d), d.max())
+    print(f"{method}: drift ref {a['drift']:.3e} ours {b['drift']:.3e}; position diff median {np.median(d):.3e} max {d.max():.3e}")
