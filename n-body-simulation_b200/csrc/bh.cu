@@ -218,9 +218,19 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
 // prefix is met ("decoupled look-back").  Tile numbers are handed out by an atomic ticket, so a tile only
 // ever waits on tiles that already started.
 // ------------------------------------------------------------------------------------------------------
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 keys per block
+#ifndef NB_SORT_THREADS
+#define NB_SORT_THREADS 256
+#endif
+#ifndef NB_SORT_ITEMS
+#define NB_SORT_ITEMS 16
+#endif
+constexpr int SORT_THREADS = NB_SORT_THREADS;
+constexpr int SORT_ITEMS = NB_SORT_ITEMS;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // keys per block
+#ifndef NB_LOOKBACK_WINDOW
+#define NB_LOOKBACK_WINDOW 8
+#endif
+constexpr int LOOKBACK_WINDOW = NB_LOOKBACK_WINDOW;
 
 template <typename K>
 __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restrict__ keys_in,
@@ -231,26 +241,15 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
     constexpr int WARPS = SORT_THREADS / 32;
     __shared__ uint32_t cnt[WARPS][256];
     __shared__ uint32_t dbase[256];
-    __shared__ uint32_t dw[WARPS];
+    __shared__ uint32_t dw[SORT_THREADS / 32 < 8 ? 8 : SORT_THREADS / 32];
     __shared__ unsigned int tile_s;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) tile_s = atomicAdd(ticket, 1u);
     for (int d = lane; d < 256; d += 32) cnt[warp][d] = 0;
-    {   // exclusive prefix of the 256 global digit counts = where each digit's bin starts in the output
-        const uint32_t v = ghist[threadIdx.x];
-        uint32_t inc = v;
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) dw[warp] = inc;
-        __syncthreads();
-        uint32_t off = inc - v;
-        for (int w = 0; w < warp; w++) off += dw[w];
-        dbase[threadIdx.x] = off;
-    }
+    // start loading this block's keys early?  The tile number is needed first.
+    __syncthreads();
     const int tile = (int)tile_s;
-    // tile order = warp-major, round-major, lane: warp w owns keys [w*512, (w+1)*512) of the tile
+    // tile order = warp-major, round-major, lane: warp w owns a contiguous 32*ITEMS run of the tile
     const int wbase = tile * SORT_TILE + warp * (32 * SORT_ITEMS);
     K key[SORT_ITEMS];
     uint32_t rank[SORT_ITEMS];
@@ -258,6 +257,33 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
     for (int k = 0; k < SORT_ITEMS; k++) {
         const int i = wbase + k * 32 + lane;
         key[k] = i < n ? keys_in[i] : (K)0;
+    }
+    if (threadIdx.x < 256 && SORT_THREADS >= 256) {
+        // exclusive prefix of the 256 global digit counts = where each digit's bin starts in the output
+        const uint32_t v = ghist[threadIdx.x];
+        uint32_t inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) dw[warp] = inc;
+        dbase[threadIdx.x] = inc - v;   // warp-local exclusive; the warp offsets are added below
+    }
+    if (SORT_THREADS < 256) {
+        // fewer threads than digits: warp 0 scans the 256 counts in 8 strips of 32
+        if (warp == 0) {
+            uint32_t carry = 0;
+            for (int s8 = 0; s8 < 8; s8++) {
+                const uint32_t v = ghist[s8 * 32 + lane];
+                uint32_t inc = v;
+                for (int o = 1; o < 32; o <<= 1) {
+                    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += t;
+                }
+                dbase[s8 * 32 + lane] = carry + inc - v;
+                carry += __shfl_sync(0xffffffffu, inc, 31);
+            }
+        }
     }
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
@@ -267,7 +293,13 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
         const unsigned act = __ballot_sync(0xffffffffu, valid);
         if (valid) {
             const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
-            const unsigned peers = __match_any_sync(act, d);
+            // lanes holding the same digit: eight ballots (MATCH.ANY is iterative and far slower on sm_100)
+            unsigned peers = act;
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                const unsigned m = __ballot_sync(act, (d >> b) & 1u);
+                peers &= ((d >> b) & 1u) ? m : ~m;
+            }
             const int leader = __ffs(peers) - 1;
             uint32_t basev = 0;
             if (lane == leader) {
@@ -280,8 +312,8 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
         __syncwarp();
     }
     __syncthreads();
-    {   // per digit: exclusive prefix over the warps of this tile, then over the tiles before it
-        const int d = threadIdx.x;
+    for (int d = threadIdx.x; d < 256; d += SORT_THREADS) {
+        // per digit: exclusive prefix over the warps of this tile, then over the tiles before it
         uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < WARPS; w++) {
@@ -292,14 +324,26 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
         volatile uint32_t* st = status;
         st[(size_t)tile * 256 + d] = (run << 2) | (tile == 0 ? 2u : 1u);
         uint32_t excl = 0;
-        for (int p = tile - 1; p >= 0; --p) {
-            uint32_t v;
-            do { v = st[(size_t)p * 256 + d]; } while ((v & 3u) == 0u);
-            excl += v >> 2;
-            if ((v & 3u) == 2u) break;
+        int p = tile - 1;
+        bool done = false;
+        while (p >= 0 && !done) {
+            uint32_t v[LOOKBACK_WINDOW];
+#pragma unroll
+            for (int j = 0; j < LOOKBACK_WINDOW; j++) v[j] = (p - j >= 0) ? st[(size_t)(p - j) * 256 + d] : 2u;
+#pragma unroll
+            for (int j = 0; j < LOOKBACK_WINDOW; j++) {
+                if (done || p - j < 0) continue;
+                uint32_t x = v[j];
+                while ((x & 3u) == 0u) x = st[(size_t)(p - j) * 256 + d];
+                excl += x >> 2;
+                if ((x & 3u) == 2u) done = true;
+            }
+            p -= LOOKBACK_WINDOW;
         }
         if (tile > 0) st[(size_t)tile * 256 + d] = ((excl + run) << 2) | 2u;
-        dbase[d] += excl;
+        uint32_t base = dbase[d] + excl;
+        if (SORT_THREADS >= 256) for (int w = 0; w < (d >> 5); w++) base += dw[w];
+        dbase[d] = base;
     }
     __syncthreads();
 #pragma unroll
