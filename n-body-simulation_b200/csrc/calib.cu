@@ -7,10 +7,17 @@ namespace {
 
 constexpr int CHAINS = 8;
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
 __global__ void __launch_bounds__(256) ffma_kernel(float* out, int iters, float a, float b, long long* cycles) {
     float x[CHAINS];
 #pragma unroll
     for (int k = 0; k < CHAINS; k++) x[k] = threadIdx.x * 1e-3f + k;
+    const unsigned long long n0 = global_ns();
     long long t0 = clock64();
     for (int i = 0; i < iters; i++) {
 #pragma unroll
@@ -19,11 +26,15 @@ __global__ void __launch_bounds__(256) ffma_kernel(float* out, int iters, float 
             for (int k = 0; k < CHAINS; k++) x[k] = fmaf(x[k], a, b);
     }
     long long t1 = clock64();
+    const unsigned long long n1 = global_ns();
     float s = 0.f;
 #pragma unroll
     for (int k = 0; k < CHAINS; k++) s += x[k];
     if (s == 123.456f) out[0] = s;
-    if (threadIdx.x == 0 && blockIdx.x == 0) cycles[0] = t1 - t0;
+    if (threadIdx.x == 0 && blockIdx.x == 0) {   // SM cycles and wall nanoseconds over the same interval
+        cycles[0] = t1 - t0;
+        cycles[1] = (long long)(n1 - n0);
+    }
 }
 
 __global__ void __launch_bounds__(256) ffma2_kernel(float* out, int iters, float a, float b) {
@@ -94,15 +105,15 @@ extern "C" int nb_calibrate(nb_context* ctx, double out[4]) {
     };
     const int it_f = 8192, it_m = 1024;
     float t_ffma = timeit(0, it_f);
-    long long cyc = 0;
-    NB_CUDA(ctx, cudaMemcpy(&cyc, d_cyc, sizeof(cyc), cudaMemcpyDeviceToHost));
+    long long cyc[2] = {0, 1};
+    NB_CUDA(ctx, cudaMemcpy(cyc, d_cyc, sizeof(cyc), cudaMemcpyDeviceToHost));
     float t_ffma2 = timeit(1, it_f);
     float t_mufu = timeit(2, it_m);
     NB_CUDA(ctx, cudaGetLastError());
     out[0] = lanes * it_f * 8.0 * CHAINS * 2.0 / (t_ffma * 1e-3) / 1e12;
     out[1] = lanes * it_f * 8.0 * CHAINS * 4.0 / (t_ffma2 * 1e-3) / 1e12;
     out[2] = lanes * it_m * 8.0 * CHAINS / (t_mufu * 1e-3) / 1e9;
-    out[3] = (double)cyc / (t_ffma * 1e-3) / 1e6;  // block 0 runs ~ the whole kernel (8 CTAs/SM resident at once)
+    out[3] = cyc[1] > 0 ? (double)cyc[0] / (double)cyc[1] * 1e3 : 0.0;   // SM clock while the FFMA loop ran, MHz
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     cudaFree(d_out);
