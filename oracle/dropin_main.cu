@@ -5,7 +5,7 @@
 // Everything else (NbodySystem.cpp, IntegrationMethods.cu, InitialConditions.cu, SimulationStats.cu, Callbacks.cpp)
 // is the reference's source in both, so the pair shows the engine dropping in behind an unchanged caller and
 // lets the energy drift of the two be compared over many steps.
-//   usage: prog <direct|bh> <n> <steps> <theta> <out.bin>
+//   usage: prog <direct|bh> <n> <steps> <theta> <out.bin> [verlet|pefrl|forestruth|euler_kd|euler_dk|vverlet] [disk|cold|merger]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -27,10 +27,28 @@ int main(int argc, char** argv) {
     ComputeMethods::ComputeMethod* compute =
         bh ? (ComputeMethods::ComputeMethod*)new ComputeMethods::BarnesHut(theta, 3, softening)
            : (ComputeMethods::ComputeMethod*)new ComputeMethods::Direct(softening);
-    auto integrator = new IntegrationMethods::Verlet_DKD();
+    const char* integ = argc > 6 ? argv[6] : "verlet";
+    const char* icname = argc > 7 ? argv[7] : "disk";
+    IntegrationMethods::IntegrationMethod* integrator;
+    if (!std::strcmp(integ, "pefrl")) integrator = new IntegrationMethods::PEFRL();                 // 4 force evaluations per step
+    else if (!std::strcmp(integ, "forestruth")) integrator = new IntegrationMethods::ForestRuth();  // 3
+    else if (!std::strcmp(integ, "euler_kd")) integrator = new IntegrationMethods::Euler_Symplectic_KD();
+    else if (!std::strcmp(integ, "euler_dk")) integrator = new IntegrationMethods::Euler_Symplectic_DK();
+    else if (!std::strcmp(integ, "vverlet")) integrator = new IntegrationMethods::Velocity_Verlet();
+    else integrator = new IntegrationMethods::Verlet_DKD();                                          // "Leapfrog"
     NbodySystem system(n, Space::R2, compute, integrator);
-    auto ic = new InitialConditions::DiskModel({0, 0}, {0, 0}, {30000, 30000}, {70000, 70000}, {0, 0});   // src/main.cu:26-32
-    system.initSystem(0, n, ic);
+    if (!std::strcmp(icname, "cold")) {          // cold collapse: the disc at rest (BASELINE.json config 4)
+        auto ic = new InitialConditions::Modules::UniformEllipsoid({0, 0}, {0, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
+        system.initSystem(0, n, ic);
+    } else if (!std::strcmp(icname, "merger")) { // two discs on a collision course (config 5)
+        auto a = new InitialConditions::DiskModel({-60000, -15000}, {40, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
+        auto b = new InitialConditions::DiskModel({60000, 15000}, {-40, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
+        system.initSystem(0, n / 2, a);
+        system.initSystem(n / 2, n - n / 2, b);
+    } else {
+        auto ic = new InitialConditions::DiskModel({0, 0}, {0, 0}, {30000, 30000}, {70000, 70000}, {0, 0});   // src/main.cu:26-32
+        system.initSystem(0, n, ic);
+    }
 
     auto [m0, k0, p0] = SimulationStats::computeStats(system.space, system.device.pos_mass, system.device.vel, n);
     system.simulate(steps, dt);

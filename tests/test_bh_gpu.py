@@ -211,3 +211,26 @@ def test_large_n_properties(pkg, oracle):
     e = _rel(got, ref)
     assert np.median(e) < 2e-3 and e.max() < 0.05, (np.median(e), e.max())
     eng.close()
+
+
+def test_sixteen_million_bodies_two_galaxies(pkg, oracle):
+    """BASELINE.json config 5 size: N = 16,777,216 two-disc merger, theta = 0.7.  The whole pipeline runs in the
+    handle's scratch (< 3 GB), the permutation is valid and a sample of bodies agrees with the FP64 direct sum
+    within the theta-error of the method."""
+    import torch
+    n = 1 << 24
+    pos = pkg.ics.two_galaxies(n)
+    eng = pkg.Engine(0, n)
+    dpos = _dev(pos)
+    acc = torch.zeros(n, 4, device="cuda")
+    eng.bh_accel(dpos, acc, 0.7, EPS, pkg.NB_BH_COUNT_WALK)
+    torch.cuda.synchronize()
+    k = eng.bh_last_counters()
+    assert k["status"] == 0 and 0 < k["nodes"] < n
+    sample = np.arange(0, n, n // 48)[:48]
+    got = acc[torch.from_numpy(sample).cuda()].cpu().numpy()
+    ref = np.concatenate([oracle.direct_f64(pos, 2, EPS, t0=int(t), nt=1) for t in sample])
+    e = _rel(got, ref)
+    assert np.median(e) < 5e-3 and e.max() < 0.1, (np.median(e), e.max())
+    info = eng.device_info()
+    eng.close()

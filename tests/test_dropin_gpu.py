@@ -15,8 +15,9 @@ REF = os.path.join(ROOT, "oracle", "_ref", "nbody_ref_prog")
 OURS = os.path.join(ROOT, "oracle", "_ref", "nbody_dropin_prog")
 
 
-def _run(prog, method, n, steps, theta, out):
-    r = subprocess.run([prog, method, str(n), str(steps), str(theta), out], capture_output=True, text=True, timeout=600)
+def _run(prog, method, n, steps, theta, out, integrator="verlet", ic="disk"):
+    r = subprocess.run([prog, method, str(n), str(steps), str(theta), out, integrator, ic], capture_output=True, text=True,
+                       timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     m = re.search(r"RESULT .*E0=(\S+) E1=(\S+) drift=(\S+) moment_drift=(\S+)", r.stdout)
     assert m, r.stdout[-2000:]
@@ -41,3 +42,21 @@ def test_energy_drift_tracks_reference_over_1000_steps(tmp_path, method, n, thet
     d = np.linalg.norm(a["pos"][:, :2] - b["pos"][:, :2], axis=1)
     assert np.quantile(d, 0.99) < 1e-4 * 30000.0, (np.median(d), d.max())
     print(f"{method}: drift ref {a['drift']:.3e} ours {b['drift']:.3e}; position diff median {np.median(d):.3e} max {d.max():.3e}")
+
+
+@pytest.mark.parametrize("integrator,ic,theta", [("pefrl", "cold", 0.5), ("forestruth", "merger", 0.7)])
+def test_other_integrators_and_initial_conditions_run_unchanged(tmp_path, integrator, ic, theta):
+    """BASELINE.json configs 4 and 5 in miniature (N = 32,768): PEFRL on a cold collapse (4 force evaluations per
+    step) and Forest-Ruth on a two-disc merger (3 per step) -- the reference's own integrator and initial-condition
+    classes, once on the reference's Barnes-Hut kernels, once on this engine."""
+    if not (os.path.exists(REF) and os.path.exists(OURS)):
+        pytest.skip("oracle/_ref drop-in programs not built (needs /root/reference at build time)")
+    n, steps = 32768, 40
+    a = _run(REF, "bh", n, steps, theta, str(tmp_path / "ref.bin"), integrator, ic)
+    b = _run(OURS, "bh", n, steps, theta, str(tmp_path / "ours.bin"), integrator, ic)
+    d = np.linalg.norm(a["pos"][:, :2] - b["pos"][:, :2], axis=1)
+    dv = np.linalg.norm(a["vel"][:, :2] - b["vel"][:, :2], axis=1)
+    vs = np.linalg.norm(a["vel"][:, :2], axis=1)
+    assert np.quantile(d, 0.999) < 1e-4 * 30000.0, (np.median(d), d.max())
+    assert np.median(dv) < 1e-3 * max(np.median(vs), 1e-3), (np.median(dv), np.median(vs))
+    assert abs(a["E1"] - b["E1"]) <= 1e-4 * abs(a["E1"])
