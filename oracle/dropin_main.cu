@@ -41,8 +41,10 @@ int main(int argc, char** argv) {
         auto ic = new InitialConditions::Modules::UniformEllipsoid({0, 0}, {0, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
         system.initSystem(0, n, ic);
     } else if (!std::strcmp(icname, "merger")) { // two discs on a collision course (config 5)
-        auto a = new InitialConditions::DiskModel({-60000, -15000}, {40, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
-        auto b = new InitialConditions::DiskModel({60000, 15000}, {-40, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
+        // (UniformEllipsoid, not DiskModel: DiskModel evaluates forces while the other half is still uninitialised,
+        //  i.e. n/2 coincident massless bodies at the origin, which the reference's tree build does not survive)
+        auto a = new InitialConditions::Modules::UniformEllipsoid({-60000, -15000}, {40, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
+        auto b = new InitialConditions::Modules::UniformEllipsoid({60000, 15000}, {-40, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
         system.initSystem(0, n / 2, a);
         system.initSystem(n / 2, n - n / 2, b);
     } else {
