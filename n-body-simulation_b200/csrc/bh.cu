@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
 #define NB_SORT_THREADS 256
 #endif
 #ifndef NB_SORT_ITEMS
-#define NB_SORT_ITEMS 16
+#define NB_SORT_ITEMS 8
 #endif
 constexpr int SORT_THREADS = NB_SORT_THREADS;
 constexpr int SORT_ITEMS = NB_SORT_ITEMS;
@@ -238,82 +238,71 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
                                                                int n, int shift, const uint32_t* __restrict__ ghist,
                                                                uint32_t* status, unsigned int* ticket,
                                                                K* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
+    static_assert(SORT_THREADS == 256, "one thread per digit");
     constexpr int WARPS = SORT_THREADS / 32;
-    __shared__ uint32_t cnt[WARPS][256];
-    __shared__ uint32_t dbase[256];
-    __shared__ uint32_t dw[SORT_THREADS / 32 < 8 ? 8 : SORT_THREADS / 32];
+    constexpr unsigned FULLM = 0xffffffffu;
+    __shared__ uint32_t cnt[WARPS][256];   // per warp and digit: count, then exclusive offset inside the tile's digit bin
+    __shared__ uint32_t dbase[256];        // global position of the tile's digit bin minus its tile-local offset
+    __shared__ uint32_t lexcl[256];        // tile-local exclusive offset of the digit bin
+    __shared__ uint32_t dw[WARPS], lw[WARPS];
     __shared__ unsigned int tile_s;
+    __shared__ K skey[SORT_TILE];
+    __shared__ int32_t sval[SORT_TILE];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) tile_s = atomicAdd(ticket, 1u);
     for (int d = lane; d < 256; d += 32) cnt[warp][d] = 0;
-    // start loading this block's keys early?  The tile number is needed first.
     __syncthreads();
     const int tile = (int)tile_s;
+    const int tile_count = min(SORT_TILE, n - tile * SORT_TILE);
     // tile order = warp-major, round-major, lane: warp w owns a contiguous 32*ITEMS run of the tile
     const int wbase = tile * SORT_TILE + warp * (32 * SORT_ITEMS);
     K key[SORT_ITEMS];
+    int32_t val[SORT_ITEMS];
     uint32_t rank[SORT_ITEMS];
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
         const int i = wbase + k * 32 + lane;
         key[k] = i < n ? keys_in[i] : (K)0;
+        val[k] = (i < n && vals_in) ? vals_in[i] : i;
     }
-    if (threadIdx.x < 256 && SORT_THREADS >= 256) {
-        // exclusive prefix of the 256 global digit counts = where each digit's bin starts in the output
+    // where each digit's bin starts in the output: exclusive prefix of the 256 global digit counts
+    uint32_t gstart;
+    {
         const uint32_t v = ghist[threadIdx.x];
         uint32_t inc = v;
+#pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            const uint32_t t = __shfl_up_sync(FULLM, inc, o);
             if (lane >= o) inc += t;
         }
         if (lane == 31) dw[warp] = inc;
-        dbase[threadIdx.x] = inc - v;   // warp-local exclusive; the warp offsets are added below
+        gstart = inc - v;
     }
-    if (SORT_THREADS < 256) {
-        // fewer threads than digits: warp 0 scans the 256 counts in 8 strips of 32
-        if (warp == 0) {
-            uint32_t carry = 0;
-            for (int s8 = 0; s8 < 8; s8++) {
-                const uint32_t v = ghist[s8 * 32 + lane];
-                uint32_t inc = v;
-                for (int o = 1; o < 32; o <<= 1) {
-                    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += t;
-                }
-                dbase[s8 * 32 + lane] = carry + inc - v;
-                carry += __shfl_sync(0xffffffffu, inc, 31);
-            }
-        }
-    }
+    // stable ranks: all warp primitives run converged with the full mask (variable masks cost a WARPSYNC each)
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
-        const int i = wbase + k * 32 + lane;
-        const bool valid = i < n;
-        rank[k] = 0;
-        const unsigned act = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
-            // lanes holding the same digit: eight ballots (MATCH.ANY is iterative and far slower on sm_100)
-            unsigned peers = act;
+        const bool valid = wbase + k * 32 + lane < n;
+        const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
+        unsigned peers = __ballot_sync(FULLM, valid);
 #pragma unroll
-            for (int b = 0; b < 8; b++) {
-                const unsigned m = __ballot_sync(act, (d >> b) & 1u);
-                peers &= ((d >> b) & 1u) ? m : ~m;
-            }
-            const int leader = __ffs(peers) - 1;
-            uint32_t basev = 0;
-            if (lane == leader) {
-                basev = cnt[warp][d];
-                cnt[warp][d] = basev + __popc(peers);
-            }
-            basev = __shfl_sync(peers, basev, leader);
-            rank[k] = basev + __popc(peers & ((1u << lane) - 1u));
+        for (int b = 0; b < 8; b++) {
+            const unsigned m = __ballot_sync(FULLM, (d >> b) & 1u);
+            peers &= ((d >> b) & 1u) ? m : ~m;
         }
+        const int leader = __ffs(peers) - 1;           // lowest valid lane holding this digit (-1 only if !valid)
+        uint32_t basev = 0;
+        if (valid && lane == leader) {
+            basev = cnt[warp][d];
+            cnt[warp][d] = basev + __popc(peers);
+        }
+        basev = __shfl_sync(FULLM, basev, leader & 31);
+        rank[k] = basev + __popc(peers & ((1u << lane) - 1u));
         __syncwarp();
     }
     __syncthreads();
-    for (int d = threadIdx.x; d < 256; d += SORT_THREADS) {
-        // per digit: exclusive prefix over the warps of this tile, then over the tiles before it
+    {
+        const int d = threadIdx.x;
+        // per digit: exclusive prefix over the warps of this tile ...
         uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < WARPS; w++) {
@@ -321,8 +310,17 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
             cnt[w][d] = run;
             run += c;
         }
+        // ... publish the tile total, then chain the prefix over the tiles before it
         volatile uint32_t* st = status;
         st[(size_t)tile * 256 + d] = (run << 2) | (tile == 0 ? 2u : 1u);
+        // tile-local exclusive offsets of the digit bins (where the bin sits in the staged, tile-sorted order)
+        uint32_t linc = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULLM, linc, o);
+            if (lane >= o) linc += t;
+        }
+        if (lane == 31) lw[warp] = linc;
         uint32_t excl = 0;
         int p = tile - 1;
         bool done = false;
@@ -341,20 +339,30 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
             p -= LOOKBACK_WINDOW;
         }
         if (tile > 0) st[(size_t)tile * 256 + d] = ((excl + run) << 2) | 2u;
-        uint32_t base = dbase[d] + excl;
-        if (SORT_THREADS >= 256) for (int w = 0; w < (d >> 5); w++) base += dw[w];
-        dbase[d] = base;
+        __syncthreads();   // dw, lw complete
+        uint32_t g = gstart + excl, l = linc - run;
+        for (int w = 0; w < warp; w++) { g += dw[w]; l += lw[w]; }
+        lexcl[d] = l;
+        dbase[d] = g - l;
     }
     __syncthreads();
+    // stage the tile in sorted order in shared memory, then write it out in runs (coalesced per digit bin)
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
-        const int i = wbase + k * 32 + lane;
-        if (i < n) {
+        if (wbase + k * 32 + lane < n) {
             const uint32_t d = (uint32_t)(key[k] >> shift) & 255u;
-            const uint32_t dst = dbase[d] + cnt[warp][d] + rank[k];
-            keys_out[dst] = key[k];
-            vals_out[dst] = vals_in ? vals_in[i] : i;
+            const uint32_t lp = lexcl[d] + cnt[warp][d] + rank[k];
+            skey[lp] = key[k];
+            sval[lp] = val[k];
         }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < tile_count; j += SORT_THREADS) {
+        const K kk = skey[j];
+        const uint32_t d = (uint32_t)(kk >> shift) & 255u;
+        const uint32_t dst = dbase[d] + j;
+        keys_out[dst] = kk;
+        vals_out[dst] = sval[j];
     }
 }
 
