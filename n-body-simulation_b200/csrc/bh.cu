@@ -58,7 +58,9 @@ struct nb_bh_state {
     float4* spos = nullptr;            // bodies in tree order: (x, y, m, -)
     D3* psum = nullptr;                // chunk-local inclusive prefix sums of (m, m x, m y)
     D3* psum_blk = nullptr;            // exclusive prefix of the chunk totals
-    int32_t* left = nullptr;           // per boundary: left extent of its node
+    int32_t* ext_a = nullptr;          // per boundary: first body of its node
+    int32_t* ext_c = nullptr;          //               first body of the child that ends at the boundary
+    int32_t* ext_r = nullptr;          //               last body of the child that starts after it
     int32_t* flag_scan = nullptr;      // chunk-local inclusive scan of leader flags
     int32_t* flag_blk = nullptr;
     float4* cblk = nullptr;            // child blocks, 4 x (cx, cy, m, acceptance threshold) per node
@@ -515,9 +517,14 @@ __device__ __forceinline__ int right_extent(const uint64_t* __restrict__ K, int 
     return good;
 }
 
-// per boundary i (between sorted bodies i and i+1): is it the leftmost separator of its node?
+// Every boundary i (between sorted bodies i and i+1) is a separator between two children of exactly one node:
+// the node at level L = cpl(K[i], K[i+1]).  Three extents describe its neighbourhood:
+//   A = first body of that node,  C = first body of the child that ends at i,  R = last body of the child that
+//   starts at i+1.
+// i is the node's first separator ("leader", gives the node its id) iff C == A.
 __global__ void __launch_bounds__(SCAN_THREADS) boundary_kernel(const uint64_t* __restrict__ K, int n,
-                                                               int32_t* __restrict__ left, int32_t* __restrict__ flag_scan,
+                                                               int32_t* __restrict__ ext_a, int32_t* __restrict__ ext_c,
+                                                               int32_t* __restrict__ ext_r, int32_t* __restrict__ flag_scan,
                                                                int32_t* __restrict__ tot) {
     int v[SCAN_ITEMS];
     const int i0 = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
@@ -526,10 +533,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) boundary_kernel(const uint64_t* 
         const int i = i0 + k;
         int f = 0;
         if (i < n - 1) {
-            const int L = cpl(K[i], K[i + 1]);
-            const int a = left_extent(K, i, L);
-            f = (a == i) || (cpl(K[a], K[i]) > L);
-            left[i] = a;
+            const uint64_t ki = K[i];
+            const int L = cpl(ki, K[i + 1]);
+            const int c = left_extent(K, i, L + 1);
+            // continue leftwards from c for the node start (cpl(K[c], K[i]) >= L+1 >= L already holds)
+            int good = c, step = 1;
+            while (good - step >= 0 && cpl(K[good - step], ki) >= L) { good -= step; step <<= 1; }
+            int bad = good - step;
+            if (bad < -1) bad = -1;
+            while (good - bad > 1) {
+                const int mid = (good + bad) >> 1;
+                if (cpl(K[mid], ki) >= L) good = mid; else bad = mid;
+            }
+            const int a = good;
+            const int r = right_extent(K, i + 1, n - 1, L + 1);
+            ext_a[i] = a;
+            ext_c[i] = c;
+            ext_r[i] = r;
+            f = (c == a);
         }
         v[k] = f;
     }
@@ -546,6 +567,9 @@ struct TreeView {
     const D3* psum_blk;
     const int32_t* flag_scan;
     const int32_t* flag_blk;
+    const int32_t* ext_a;
+    const int32_t* ext_c;
+    const int32_t* ext_r;
     int n;
 };
 
@@ -554,6 +578,15 @@ __device__ __forceinline__ D3 prefix_incl(const TreeView& t, int i) {  // sum ov
     return D3{a.m + b.m, a.mx + b.mx, a.my + b.my};
 }
 __device__ __forceinline__ int flag_incl(const TreeView& t, int i) { return t.flag_scan[i] + t.flag_blk[i >> SCAN_SHIFT]; }
+__device__ __forceinline__ int level_at(const TreeView& t, int i) {   // d(i), -1 outside [0, n-1)
+    return (i < 0 || i >= t.n - 1) ? -1 : cpl(t.K[i], t.K[i + 1]);
+}
+// id of the node that separator j (level L) belongs to: walk back over the node's earlier separators to its leader
+__device__ __forceinline__ int node_of(const TreeView& t, int j, int L) {
+    if (L >= MAX_LEVEL) j = t.ext_a[j];                  // bucket: every boundary separates, the first one leads
+    else while (t.ext_c[j] != t.ext_a[j]) j = t.ext_c[j] - 1;   // at most three hops
+    return flag_incl(t, j) - 1;
+}
 
 // Acceptance threshold (squared size / theta^2) a cell that splits at level L is tested with:
 // s0 * 0.25^(L-1), s0 = (dim_size/theta)^2 (src/BarnesHutKernels.cu:403-404,411; the scaling is exact).
@@ -563,81 +596,84 @@ __device__ __forceinline__ float threshold_of(float s0, int L) {
     return s0 * __int_as_float((127 - 2 * (L - 1)) << 23);
 }
 
-__global__ void __launch_bounds__(256) emit_kernel(TreeView t, const int32_t* __restrict__ left,
-                                                  const float4* __restrict__ bounds, float theta,
-                                                  float4* __restrict__ cblk, uint4* __restrict__ clink,
+// One thread per separator, no searches: it writes the body children next to it and the empty slots between its
+// two children; the LAST separator of a node (the only one that knows the node's whole range) writes the node's
+// own record -- monopole from the FP64 prefix sums, acceptance threshold, link -- into its parent's child block.
+__global__ void __launch_bounds__(256) emit_kernel(TreeView t, const float4* __restrict__ bounds, float theta,
+                                                  float4* __restrict__ cblk, uint32_t* __restrict__ clink,
                                                   int32_t* __restrict__ node_first, int32_t* __restrict__ node_last,
                                                   int8_t* __restrict__ node_level, int8_t* __restrict__ node_top,
                                                   int32_t* __restrict__ root, float4* __restrict__ root_rec) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= t.n - 1) return;
-    const int incl = flag_incl(t, i);
-    const int prev = i > 0 ? flag_incl(t, i - 1) : 0;
-    if (incl == prev) return;          // not a leader
-    const int id = prev;               // exclusive scan = node id
     const uint64_t* K = t.K;
-    const int L = cpl(K[i], K[i + 1]);
-    const int a = left[i];
-    const int b = right_extent(K, i + 1, t.n - 1, L);
-    node_first[id] = a;
+    const uint64_t ki = K[i], kn = K[i + 1];
+    const int L = cpl(ki, kn);
+    const int a = t.ext_a[i], c = t.ext_c[i], r = t.ext_r[i];
+    const int id = node_of(t, i, L);
+    const bool first = (c == a);
+    const bool last = (r == t.n - 1) || (cpl(K[r], K[r + 1]) < L);
+    if (first) {
+        node_first[id] = a;
+        node_level[id] = (int8_t)L;
+    }
+    if (L < MAX_LEVEL) {
+        float4* blk = cblk + 4 * (size_t)id;
+        uint32_t* lnk = clink + 4 * (size_t)id;
+        const int ql = (int)((ki >> (62 - 2 * L)) & 3ull), qn = (int)((kn >> (62 - 2 * L)) & 3ull);   // key digits, ql < qn
+        const float4 empty = make_float4(FAR_AWAY, FAR_AWAY, 0.f, 0.f);   // massless, always "accepted", adds exactly 0
+        // empty slots: before the first child, between my two children, after the last child (slot = digit ^ 2)
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if ((q > ql && q < qn) || (first && q < ql) || (last && q > qn)) {
+                blk[q ^ 2] = empty;
+                lnk[q ^ 2] = LINK_EMPTY;
+            }
+        }
+        if (c == i) {              // the child that ends at i is the single body i
+            const float4 p = t.spos[i];
+            blk[ql ^ 2] = make_float4(p.x, p.y, p.z, 0.f);
+            lnk[ql ^ 2] = LINK_BODY;
+        }
+        if (last && r == i + 1) {  // the last child is the single body i+1
+            const float4 p = t.spos[i + 1];
+            blk[qn ^ 2] = make_float4(p.x, p.y, p.z, 0.f);
+            lnk[qn ^ 2] = LINK_BODY;
+        }
+    }
+    if (!last) return;
+    // ---- the node [a, r] as a whole ------------------------------------------------------------------------
+    const int b = r;
     node_last[id] = b;
-    node_level[id] = (int8_t)L;
+    if (L >= MAX_LEVEL)      // bucket: all keys equal; the walk sums bodies [a, b] directly
+        cblk[4 * (size_t)id] = make_float4(__int_as_float(a), __int_as_float(b - a + 1), 0.f, 0.f);
     const float4 bb = *bounds;
     const float dim_size = fmaxf(bb.z - bb.x, bb.w - bb.y);       // src/BarnesHutKernels.cu:384
     float s0 = dim_size / theta;                                   // :403
     s0 *= s0;                                                      // :404
-    if (a == 0 && b == t.n - 1) {
+    const D3 hi = prefix_incl(t, b);
+    D3 lo = D3{0.0, 0.0, 0.0};
+    if (a > 0) lo = prefix_incl(t, a - 1);
+    const double m = hi.m - lo.m;
+    float cx = 0.f, cy = 0.f;   // centre_of_mass (src/BarnesHutKernels.cu:367-379): only where mass > 0
+    if (m > 0.0) { cx = (float)((hi.mx - lo.mx) / m); cy = (float)((hi.my - lo.my) / m); }
+    const float4 rec = make_float4(cx, cy, (float)m, threshold_of(s0, L));
+    const uint32_t link = (uint32_t)id | (L >= MAX_LEVEL ? LINK_BUCKET : 0u);
+    const int dl = level_at(t, a - 1), dr = level_at(t, b);
+    if (dl < 0 && dr < 0) {       // the root cell
         root[0] = id;
         node_top[id] = 0;
-        const D3 all = prefix_incl(t, t.n - 1);
-        float cx = 0.f, cy = 0.f;
-        if (all.m > 0.0) { cx = (float)(all.mx / all.m); cy = (float)(all.my / all.m); }
-        root_rec[0] = make_float4(cx, cy, (float)all.m, threshold_of(s0, L));
-        root_rec[1] = make_float4(__uint_as_float((uint32_t)id | (L >= MAX_LEVEL ? LINK_BUCKET : 0u)), 0.f, 0.f, 0.f);
-    }
-    float4* blk = cblk + 4 * (size_t)id;
-    if (L >= MAX_LEVEL) {  // bucket: all keys equal; the walk sums bodies [a, b] directly
-        blk[0] = make_float4(__int_as_float(a), __int_as_float(b - a + 1), 0.f, 0.f);
+        root_rec[0] = rec;
+        root_rec[1] = make_float4(__uint_as_float(link), 0.f, 0.f, 0.f);
         return;
     }
-    float4 rec[4];
-    uint32_t lk[4];
-#pragma unroll
-    for (int s = 0; s < 4; s++) {
-        rec[s] = make_float4(FAR_AWAY, FAR_AWAY, 0.f, 0.f);   // empty: massless, always "accepted", adds exactly 0
-        lk[s] = LINK_EMPTY;
-    }
-    int c0 = a;
-    while (c0 <= b) {
-        const int e = right_extent(K, c0, b, L + 1);
-        const int slot = (int)((K[c0] >> (62 - 2 * L)) & 3ull) ^ 2;   // path = digit ^ 2
-        float4 r;
-        uint32_t link;
-        if (e == c0) {
-            const float4 p = t.spos[c0];
-            r = make_float4(p.x, p.y, p.z, 0.f);
-            link = LINK_BODY;
-        } else {
-            const D3 hi = prefix_incl(t, e);
-            D3 lo = D3{0.0, 0.0, 0.0};
-            if (c0 > 0) lo = prefix_incl(t, c0 - 1);
-            const double m = hi.m - lo.m;
-            float cx = 0.f, cy = 0.f;   // centre_of_mass (src/BarnesHutKernels.cu:367-379): only where mass > 0
-            if (m > 0.0) { cx = (float)((hi.mx - lo.mx) / m); cy = (float)((hi.my - lo.my) / m); }
-            const int Lc = cpl(K[c0], K[e]);
-            const int e1 = right_extent(K, c0, e, Lc + 1);            // end of the child's first child = its leader boundary
-            const int cid = flag_incl(t, e1) - 1;
-            node_top[cid] = (int8_t)(L + 1);
-            r = make_float4(cx, cy, (float)m, threshold_of(s0, Lc));
-            link = (uint32_t)cid | (Lc >= MAX_LEVEL ? LINK_BUCKET : 0u);
-        }
-#pragma unroll
-        for (int s = 0; s < 4; s++) if (s == slot) { rec[s] = r; lk[s] = link; }
-        c0 = e + 1;
-    }
-#pragma unroll
-    for (int s = 0; s < 4; s++) blk[s] = rec[s];
-    clink[id] = make_uint4(lk[0], lk[1], lk[2], lk[3]);
+    const int Lp = max(dl, dr);
+    const int p = (dl >= dr) ? a - 1 : b;           // a separator of the parent, next to this node
+    const int pid = node_of(t, p, Lp);
+    const int slot = (int)((K[a] >> (62 - 2 * Lp)) & 3ull) ^ 2;
+    node_top[id] = (int8_t)(Lp + 1);
+    cblk[4 * (size_t)pid + slot] = rec;
+    clink[4 * (size_t)pid + slot] = link;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -925,7 +961,7 @@ void free_state(nb_bh_state* st) {
     if (!st) return;
     void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
                     st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->ghist, st->clink, st->spos, st->psum, st->psum_blk,
-                    st->left, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
+                    st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
                     st->node_top, st->root, st->root_rec, st->counters};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -968,7 +1004,9 @@ int ensure_state(nb_context* ctx, int n) {
     rc |= alloc(ctx, &st->spos, cap);
     rc |= alloc(ctx, &st->psum, cap);
     rc |= alloc(ctx, &st->psum_blk, chunks);
-    rc |= alloc(ctx, &st->left, cap);
+    rc |= alloc(ctx, &st->ext_a, cap);
+    rc |= alloc(ctx, &st->ext_c, cap);
+    rc |= alloc(ctx, &st->ext_r, cap);
     rc |= alloc(ctx, &st->flag_scan, cap);
     rc |= alloc(ctx, &st->flag_blk, chunks);
     rc |= alloc(ctx, &st->cblk, 4 * cap);
@@ -1024,12 +1062,13 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
                                                                st->psum_blk);
         scan_totals_kernel<D3><<<1, 1024, 0, stream>>>(st->psum_blk, chunks);
         const int bchunks = (n - 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
-        boundary_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->left, st->flag_scan, st->flag_blk);
+        boundary_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk);
         scan_totals_kernel<int><<<1, 1024, 0, stream>>>(st->flag_blk, bchunks);
-        TreeView tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, n};
-        emit_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->left, st->bounds, theta, st->cblk, st->clink,
-                                                             st->node_first, st->node_last, st->node_level, st->node_top,
-                                                             st->root, st->root_rec);
+        TreeView tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, st->ext_a, st->ext_c, st->ext_r, n};
+        emit_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->bounds, theta, st->cblk,
+                                                             reinterpret_cast<uint32_t*>(st->clink), st->node_first,
+                                                             st->node_last, st->node_level, st->node_top, st->root,
+                                                             st->root_rec);
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
