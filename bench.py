@@ -344,6 +344,22 @@ def main():
                     bh["e2e"] = {"value": ksteps / (time.perf_counter() - t0), "unit": "steps/s",
                                  "h2d_bytes_per_step": nb * 16, "d2h_bytes_per_step": nb * 16,
                                  "call": "nb_bh_accel_host"}
+                    # theta-error of the result against the FP64 direct sum on a sample of bodies, and the host baseline
+                    if not args.skip_cpu:
+                        oracle = graft.load_oracle()
+                        sample = np.arange(0, nb, nb // 256)[:256]
+                        ref64 = np.concatenate([oracle.direct_f64(p2_h, 2, EPS, t0=int(t), nt=1) for t in sample])[:, :2]
+                        ours = a2[torch.from_numpy(sample).to(dev)].cpu().numpy()[:, :2].astype(np.float64)
+                        err = np.linalg.norm(ours - ref64, axis=1) / np.linalg.norm(ref64, axis=1)
+                        bh["theta_error_vs_fp64"] = {"median": float(np.median(err)), "p99": float(np.quantile(err, 0.99)),
+                                                     "max": float(err.max()), "sample": 256}
+                        t0 = time.perf_counter()
+                        ob = oracle.bh_accel(p2_h, THETA, EPS)
+                        dt_cpu = time.perf_counter() - t0
+                        oerr = np.linalg.norm(ob["acc"][sample][:, :2] - ref64, axis=1) / np.linalg.norm(ref64, axis=1)
+                        bh["cpu_baseline"] = {"value": 1.0 / dt_cpu, "unit": "steps/s", "cores": oracle.max_threads(), "kind": "port",
+                                              "sample": "one full force evaluation at N=1048576 (serial-equivalent tree insert, OpenMP walk)",
+                                              "theta_error_median": float(np.median(oerr))}
                     so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
                     if os.path.exists(so) and not args.skip_refcuda:
                         import ctypes as C
@@ -369,7 +385,13 @@ def main():
                             tms.append((time.perf_counter() - t0) * 1e3)
                         ref_ms = min(tms[1:])
                         d = (ra[:, :2] - a2[:, :2]).norm(dim=1) / ra[:, :2].norm(dim=1)
+                        ref_err = None
+                        if not args.skip_cpu:
+                            rr = ra[torch.from_numpy(sample).to(dev)].cpu().numpy()[:, :2].astype(np.float64)
+                            e2 = np.linalg.norm(rr - ref64, axis=1) / np.linalg.norm(ref64, axis=1)
+                            ref_err = {"median": float(np.median(e2)), "p99": float(np.quantile(e2, 0.99)), "max": float(e2.max())}
                         bh["reference_cuda_bh"] = {"steps_per_s": 1e3 / ref_ms, "ms": ref_ms, "speedup": ref_ms / bh_ms,
+                                                   "theta_error_vs_fp64": ref_err,
                                                    "acc_rel_diff_median": float(d.median()),
                                                    "acc_rel_diff_p99": float(d.quantile(0.99)),
                                                    "what": "unmodified src/BarnesHutKernels.cu (sm_100), knodes=3, same box"}
