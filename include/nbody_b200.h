@@ -156,6 +156,36 @@ int nb_verlet_dkd_drift(nb_context* ctx, float* pos, const float* vel, int begin
 int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const float* acc, int begin, int count,
                              float dt, void* stream);
 
+/* Any kick/drift kernel of the reference's steppers (src/IntegrationMethods.cu:13-349) on a target slice: an
+ * optional velocity update followed by an optional position update that uses the new velocity.  The kinds
+ * name the reference's expression types (a double literal promotes the product to FP64, rounded once):
+ *   NB_KICK_F32       vel += dt*acc                      Euler KD/DK :16-18,52-54, Verlet DKD :84-86
+ *   NB_KICK_HALF_F64  vel += dt*0.5*acc                  Verlet KDK :113-115,126-128
+ *   NB_KICK_COEF_F64  vel += kick_coef*acc               PEFRL :293-295.. (kick_coef = the double c*dt)
+ *   NB_KICK_DTA_F64   vel += dt*acc*kick_coef            Forest-Ruth :214-216..
+ *   NB_KICK_MEAN_F64  vel += 0.5*dt*(acc+acc_prev)       Velocity Verlet :162-164
+ *   NB_DRIFT_F32      pos += vel*dt                      Euler :20-22,43-45, Verlet KDK :117-119
+ *   NB_DRIFT_HALF_F64 pos += vel*(dt*0.5)                Verlet DKD :76-78,88-90
+ *   NB_DRIFT_COEF_F64 pos += drift_coef*vel              PEFRL :281-283..
+ *   NB_DRIFT_VDT_F64  pos += vel*dt*drift_coef*0.5       Forest-Ruth :203-205..
+ *   NB_DRIFT_VV_F64   pos += vel*dt + acc*0.5*dt*dt      Velocity Verlet :152-154
+ * pos is the full float4[n] array, vel/acc/acc_prev are slice-local float4[count]. */
+#define NB_KICK_NONE 0
+#define NB_KICK_F32 1
+#define NB_KICK_HALF_F64 2
+#define NB_KICK_COEF_F64 3
+#define NB_KICK_DTA_F64 4
+#define NB_KICK_MEAN_F64 5
+#define NB_DRIFT_NONE 0
+#define NB_DRIFT_F32 1
+#define NB_DRIFT_HALF_F64 2
+#define NB_DRIFT_COEF_F64 3
+#define NB_DRIFT_VDT_F64 4
+#define NB_DRIFT_VV_F64 5
+int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, const float* acc, const float* acc_prev, int begin,
+                         int count, float dt, int kick_kind, double kick_coef, int drift_kind, double drift_coef,
+                         void* stream);
+
 /* ---- calibration --------------------------------------------------------------------------------- */
 
 /* Measures this GPU's FP32 roofline denominators with register-resident microbenchmarks:

@@ -26,6 +26,7 @@ ABI_SYMBOLS = [
     "nb_direct_last_launch",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
+    "nb_integrate_substep",
 ]
 
 
@@ -64,6 +65,7 @@ def lib():
         L.nb_calibrate.argtypes = [vp, C.POINTER(C.c_double)]
         L.nb_verlet_dkd_drift.argtypes = [vp, vp, vp, i, i, f, vp]
         L.nb_verlet_dkd_kick_drift.argtypes = [vp, vp, vp, vp, i, i, f, vp]
+        L.nb_integrate_substep.argtypes = [vp, vp, vp, vp, vp, i, i, f, i, C.c_double, i, C.c_double, vp]
         _lib = L
     return _lib
 
@@ -195,6 +197,13 @@ class Engine:
         self._check(lib().nb_verlet_dkd_kick_drift(self._h, pos.data_ptr(), vel.data_ptr(), acc.data_ptr(), begin,
                                                    count, dt, _stream_ptr(stream)), "nb_verlet_dkd_kick_drift")
 
+    def integrate_substep(self, pos, vel, acc, begin, count, dt, kick=0, kick_coef=0.0, drift=0, drift_coef=0.0,
+                          acc_prev=None, stream=None):
+        self._check(lib().nb_integrate_substep(self._h, pos.data_ptr(), vel.data_ptr(), acc.data_ptr(),
+                                               acc_prev.data_ptr() if acc_prev is not None else None, begin, count, dt,
+                                               kick, kick_coef, drift, drift_coef, _stream_ptr(stream)),
+                    "nb_integrate_substep")
+
     def calibrate(self):
         out = (C.c_double * 4)()
         self._check(lib().nb_calibrate(self._h, out), "nb_calibrate")
@@ -231,3 +240,5 @@ def _host_ptr(a):
 from .system import R2, R3, ComputeMethods, NbodySystem  # noqa: E402,F401
 from . import ics  # noqa: E402,F401
 from . import shard  # noqa: E402,F401
+from . import integrators  # noqa: E402,F401
+from .integrators import IntegrationMethods  # noqa: E402,F401

@@ -70,3 +70,80 @@ int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const floa
     return NB_OK;
 }
 }
+
+// ------------------------------------------------------------------------------------------------------
+// General kick/drift sub-step: every elementwise kernel of src/IntegrationMethods.cu:13-349 is "an optional
+// velocity update followed by an optional position update that uses the new velocity", on a target slice.
+// The kinds reproduce the reference's mixed FP32/FP64 expression types: a `double`
+// literal or coefficient promotes the whole product to FP64 and the result is rounded once on the `+=`.
+// ------------------------------------------------------------------------------------------------------
+namespace {
+
+struct SubstepArgs {
+    int kick, drift;
+    float dt;
+    double ck, cd;
+};
+
+__device__ __forceinline__ float kick1(const SubstepArgs& s, float v, float a, float ap) {
+    switch (s.kick) {
+        case NB_KICK_F32:       return fmaf(s.dt, a, v);                                          // vel += dt * acc
+        case NB_KICK_HALF_F64:  return (float)__fma_rn((double)s.dt * 0.5, (double)a, (double)v);  // vel += dt * 0.5 * acc
+        case NB_KICK_COEF_F64:  return (float)__fma_rn(s.ck, (double)a, (double)v);                // vel += (c*dt) * acc      (PEFRL)
+        case NB_KICK_DTA_F64:   return (float)__fma_rn((double)(s.dt * a), s.ck, (double)v);       // vel += dt * acc * c      (Forest-Ruth)
+        case NB_KICK_MEAN_F64:  return (float)__fma_rn(0.5 * (double)s.dt, (double)(a + ap), (double)v);  // vel += 0.5*dt*(acc+prev)
+        default:                return v;
+    }
+}
+__device__ __forceinline__ float drift1g(const SubstepArgs& s, float p, float v, float a) {
+    switch (s.drift) {
+        case NB_DRIFT_F32:      return fmaf(v, s.dt, p);                                           // pos += vel * dt
+        case NB_DRIFT_HALF_F64: return (float)__fma_rn((double)v, (double)s.dt * 0.5, (double)p);   // pos += vel * (dt * 0.5)
+        case NB_DRIFT_COEF_F64: return (float)__fma_rn(s.cd, (double)v, (double)p);                 // pos += (c*dt) * vel      (PEFRL)
+        case NB_DRIFT_VDT_F64:  return (float)__fma_rn(__dmul_rn((double)(v * s.dt), s.cd), 0.5, (double)p);   // pos += vel*dt*c*0.5 (Forest-Ruth)
+        case NB_DRIFT_VV_F64:   // pos += vel*dt + acc*0.5*dt*dt   (Velocity Verlet)
+            return (float)((double)p + ((double)(v * s.dt) + __dmul_rn(__dmul_rn((double)a * 0.5, (double)s.dt), (double)s.dt)));
+        default:                return p;
+    }
+}
+
+__global__ void substep_kernel(float4* __restrict__ pos, float4* __restrict__ vel, const float4* __restrict__ acc,
+                               const float4* __restrict__ acc_prev, int begin, int count, SubstepArgs s) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float4 v = vel[i];
+    const float4 a = acc[i];
+    float4 ap = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (s.kick == NB_KICK_MEAN_F64) ap = acc_prev[i];
+    if (s.kick != NB_KICK_NONE) {
+        v.x = kick1(s, v.x, a.x, ap.x);
+        v.y = kick1(s, v.y, a.y, ap.y);
+        v.z = kick1(s, v.z, a.z, ap.z);
+        vel[i] = v;
+    }
+    if (s.drift != NB_DRIFT_NONE) {
+        float4 p = pos[begin + i];
+        p.x = drift1g(s, p.x, v.x, a.x);
+        p.y = drift1g(s, p.y, v.y, a.y);
+        p.z = drift1g(s, p.z, v.z, a.z);
+        pos[begin + i] = p;
+    }
+}
+
+}  // namespace
+
+extern "C" int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, const float* acc, const float* acc_prev, int begin,
+                                    int count, float dt, int kick_kind, double kick_coef, int drift_kind, double drift_coef,
+                                    void* stream) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (begin < 0 || count < 0) return nb_fail(ctx, NB_ERR_INVALID, "bad slice");
+    if (kick_kind < 0 || kick_kind > NB_KICK_MEAN_F64 || drift_kind < 0 || drift_kind > NB_DRIFT_VV_F64)
+        return nb_fail(ctx, NB_ERR_INVALID, "unknown kick/drift kind");
+    if (kick_kind == NB_KICK_MEAN_F64 && !acc_prev) return nb_fail(ctx, NB_ERR_INVALID, "NB_KICK_MEAN_F64 needs acc_prev");
+    if (count == 0) return NB_OK;
+    SubstepArgs s{kick_kind, drift_kind, dt, kick_coef, drift_coef};
+    substep_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, (const float4*)acc,
+                                                                         (const float4*)acc_prev, begin, count, s);
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
