@@ -186,6 +186,16 @@ int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, const float* a
                          int count, float dt, int kick_kind, double kick_coef, int drift_kind, double drift_coef,
                          void* stream);
 
+/* ---- diagnostics (callers of the path) ------------------------------------- */
+
+/* SimulationStats::computeStats (src/SimulationStats.cu:7-27) for the bodies [target_begin, target_begin +
+ * target_count) against all n bodies: out[0] = sum m|v| ("moment"), out[1] = kinetic energy, out[2] = FP64
+ * potential energy with the reference's formula (every ordered pair including i = j, epsilon 1e-6, 1/r law).
+ * pos: device float4[n]; vel: device float4[target_count] (slice-local).  Sums of slices add up to the
+ * whole-system values (sharding: all-reduce the three doubles).  Synchronises `stream`; out is host memory. */
+int nb_stats(nb_context* ctx, const float* pos, const float* vel, int n, int target_begin, int target_count, int dim,
+             double out[3], void* stream);
+
 /* ---- calibration --------------------------------------------------------------------------------- */
 
 /* Measures this GPU's FP32 roofline denominators with register-resident microbenchmarks:

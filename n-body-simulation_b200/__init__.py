@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "nb_direct_last_launch",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
-    "nb_integrate_substep",
+    "nb_integrate_substep", "nb_stats",
 ]
 
 
@@ -65,6 +65,7 @@ def lib():
         L.nb_calibrate.argtypes = [vp, C.POINTER(C.c_double)]
         L.nb_verlet_dkd_drift.argtypes = [vp, vp, vp, i, i, f, vp]
         L.nb_verlet_dkd_kick_drift.argtypes = [vp, vp, vp, vp, i, i, f, vp]
+        L.nb_stats.argtypes = [vp, vp, vp, i, i, i, i, C.POINTER(C.c_double), vp]
         L.nb_integrate_substep.argtypes = [vp, vp, vp, vp, vp, i, i, f, i, C.c_double, i, C.c_double, vp]
         _lib = L
     return _lib
@@ -203,6 +204,15 @@ class Engine:
                                                acc_prev.data_ptr() if acc_prev is not None else None, begin, count, dt,
                                                kick, kick_coef, drift, drift_coef, _stream_ptr(stream)),
                     "nb_integrate_substep")
+
+    def stats(self, pos, vel, dim, target_begin=0, target_count=None, stream=None):
+        """(moment, kinetic energy, potential energy) of a target slice, SimulationStats::computeStats."""
+        n = pos.shape[0]
+        cnt = n - target_begin if target_count is None else target_count
+        out = (C.c_double * 3)()
+        self._check(lib().nb_stats(self._h, pos.data_ptr(), vel.data_ptr(), n, target_begin, cnt, dim, out,
+                                   _stream_ptr(stream)), "nb_stats")
+        return out[0], out[1], out[2]
 
     def calibrate(self):
         out = (C.c_double * 4)()

@@ -44,6 +44,7 @@ int nb_destroy(nb_context* ctx) {
     nb_bh_destroy(ctx);
     if (ctx->partial) cudaFree(ctx->partial);
     if (ctx->tile_flags) cudaFree(ctx->tile_flags);
+    if (ctx->stats) cudaFree(ctx->stats);
     if (ctx->dev_pos) cudaFree(ctx->dev_pos);
     if (ctx->dev_acc) cudaFree(ctx->dev_acc);
     if (ctx->host_stream) cudaStreamDestroy(ctx->host_stream);

@@ -21,6 +21,8 @@ struct nb_context {
     size_t partial_bytes = 0;
     void* tile_flags = nullptr;   // [0..64): m_ref, 1/m_ref; then one byte per source tile (mass hoisting)
     size_t tile_flags_bytes = 0;
+    void* stats = nullptr;        // SimulationStats partial sums (stats.cu)
+    size_t stats_bytes = 0;
     void* dev_pos = nullptr;      // staging for the *_host entry points
     void* dev_acc = nullptr;
     size_t dev_pos_bytes = 0, dev_acc_bytes = 0;

@@ -122,3 +122,32 @@ def test_sharded_system_barnes_hut_leapfrog(engine, pkg):
     engine.verlet_dkd_kick_drift(p2, v2, a2, 0, n, 0.001)
     torch.cuda.synchronize()
     assert torch.equal(sysm.pos, p2) and torch.equal(sysm.vel, v2)
+
+
+def test_simulation_stats_match_the_reference_formulae(engine, pkg):
+    """nb_stats against a NumPy FP64 restatement of src/SimulationStats.cu:29-90 (pairs counted twice, i = j included,
+    epsilon 1e-6), in 2D and 3D, whole system and as the sum of ragged slices."""
+    import torch
+    n = 3000
+    pos = pkg.ics.uniform_disk(n, seed=71, z_half_height=3000.0)
+    rng = np.random.default_rng(4)
+    vel = (rng.standard_normal((n, 4)) * 200).astype(np.float32)
+    p64, v64, m = pos[:, :3].astype(np.float64), vel.astype(np.float64), pos[:, 3].astype(np.float64)
+    d2 = ((p64[:, None, :] - p64[None, :, :]) ** 2).sum(-1) + 1e-6
+    pe = -(m[:, None] * m[None, :] / np.sqrt(d2)).sum()
+    dpos, dvel = torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda()
+    for dim in (2, 3):
+        if dim == 3:
+            v = np.sqrt((v64[:, :3] ** 2).sum(1))
+        else:
+            v = np.sqrt((vel[:, 0] * vel[:, 0] + vel[:, 1] * vel[:, 1]).astype(np.float64))
+        want = ((v * m).sum(), (0.5 * v * v * m).sum(), pe)
+        got = engine.stats(dpos, dvel, dim)
+        # 2D: the reference squares and adds in FP32 before the sqrt (:34); the FMA contraction of the device differs
+        # from NumPy's two roundings by an FP32 ulp per body
+        rt = 1e-12 if dim == 3 else 1e-7
+        assert np.allclose(got[:2], want[:2], rtol=rt) and np.isclose(got[2], want[2], rtol=1e-12), (got, want)
+        parts = np.zeros(3)
+        for a, b in ((0, 1), (1, 1300), (1300, n)):
+            parts += np.array(engine.stats(dpos, dvel[a:b].contiguous(), dim, a, b - a))
+        assert np.allclose(parts[:2], want[:2], rtol=rt) and np.isclose(parts[2], want[2], rtol=1e-12)
