@@ -250,5 +250,6 @@ def _host_ptr(a):
 from .system import R2, R3, ComputeMethods, NbodySystem  # noqa: E402,F401
 from . import ics  # noqa: E402,F401
 from . import shard  # noqa: E402,F401
+from . import checkpoint  # noqa: E402,F401
 from . import integrators  # noqa: E402,F401
 from .integrators import IntegrationMethods  # noqa: E402,F401

@@ -5,11 +5,13 @@
 // Everything else (NbodySystem.cpp, IntegrationMethods.cu, InitialConditions.cu, SimulationStats.cu, Callbacks.cpp)
 // is the reference's source in both, so the pair shows the engine dropping in behind an unchanged caller and
 // lets the energy drift of the two be compared over many steps.
-//   usage: prog <direct|bh> <n> <steps> <theta> <out.bin> [verlet|pefrl|forestruth|euler_kd|euler_dk|vverlet] [disk|cold|merger]
+//   usage: prog <direct|bh> <n> <steps> <theta> <out.bin> [verlet|pefrl|forestruth|euler_kd|euler_dk|vverlet] [disk|cold|merger|load:<file.params>] [checkpoint_dir]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <tuple>
+#include <string>
+#include <unistd.h>
 
 #include "NbodySystem.h"
 
@@ -19,7 +21,7 @@ int main(int argc, char** argv) {
         return 2;
     }
     const bool bh = std::strcmp(argv[1], "bh") == 0;
-    const int n = std::atoi(argv[2]);
+    int n = std::atoi(argv[2]);
     const int steps = std::atoi(argv[3]);
     const float theta = (float)std::atof(argv[4]);
     const float softening = 1.01f, dt = 0.001f;   // src/main.cu:7,12
@@ -36,8 +38,18 @@ int main(int argc, char** argv) {
     else if (!std::strcmp(integ, "euler_dk")) integrator = new IntegrationMethods::Euler_Symplectic_DK();
     else if (!std::strcmp(integ, "vverlet")) integrator = new IntegrationMethods::Velocity_Verlet();
     else integrator = new IntegrationMethods::Verlet_DKD();                                          // "Leapfrog"
-    NbodySystem system(n, Space::R2, compute, integrator);
-    if (!std::strcmp(icname, "cold")) {          // cold collapse: the disc at rest (BASELINE.json config 4)
+    const bool load = !std::strncmp(icname, "load:", 5);
+    // either the plain constructor + an initial-condition generator, or the reference's own checkpoint loader
+    // (src/NbodySystem.cpp:27-70), which takes N from the file size
+    NbodySystem* sysp = load ? new NbodySystem(std::string(icname + 5), Space::R2, compute, integrator)
+                             : new NbodySystem(n, Space::R2, compute, integrator);
+    NbodySystem& system = *sysp;
+    if (argc > 8) {   // run inside <checkpoint_dir> and let the reference's CheckpointSaver write configs/run_<steps>.params
+        if (chdir(argv[8]) != 0) return 3;
+        system.addCallback(new Callbacks::CheckpointSaver(steps, "run"));
+    }
+    if (load) {
+    } else if (!std::strcmp(icname, "cold")) {          // cold collapse: the disc at rest (BASELINE.json config 4)
         auto ic = new InitialConditions::Modules::UniformEllipsoid({0, 0}, {0, 0}, {30000, 30000}, {70000, 70000}, {0, 0});
         system.initSystem(0, n, ic);
     } else if (!std::strcmp(icname, "merger")) { // two discs on a collision course (config 5)
@@ -52,6 +64,7 @@ int main(int argc, char** argv) {
         system.initSystem(0, n, ic);
     }
 
+    n = system.N;
     auto [m0, k0, p0] = SimulationStats::computeStats(system.space, system.device.pos_mass, system.device.vel, n);
     system.simulate(steps, dt);
     cudaDeviceSynchronize();

@@ -60,3 +60,30 @@ def test_other_integrators_and_initial_conditions_run_unchanged(tmp_path, integr
     assert np.quantile(d, 0.999) < 1e-4 * 30000.0, (np.median(d), d.max())
     assert np.median(dv) < 1e-3 * max(np.median(vs), 1e-3), (np.median(dv), np.median(vs))
     assert abs(a["E1"] - b["E1"]) <= 1e-4 * abs(a["E1"])
+
+
+def test_checkpoints_are_interchangeable_with_the_reference(tmp_path, pkg):
+    """A .params file written by the reference's own CheckpointSaver is read by checkpoint.load_params, and one
+    written by checkpoint.save_params is loaded by the reference's NbodySystem(configPath) constructor."""
+    if not (os.path.exists(REF) and os.path.exists(OURS)):
+        pytest.skip("oracle/_ref drop-in programs not built (needs /root/reference at build time)")
+    n, steps = 4096, 10
+    work = tmp_path / "ck"
+    work.mkdir()
+    out = str(tmp_path / "state.bin")
+    r = subprocess.run([REF, "direct", str(n), str(steps), "0.5", out, "verlet", "disk", str(work)], capture_output=True,
+                       text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-1000:]
+    state = np.fromfile(out, dtype=np.float32).reshape(2, n, 4)
+    assert open(work / "configs" / "run.json").read() == pkg.checkpoint.config_json_text(n, True)
+    pos, vel = pkg.checkpoint.load_params(str(work / "configs" / f"run_{steps}.params"))
+    assert np.array_equal(pos, state[0]) and np.array_equal(vel[:, :3], state[1][:, :3])
+    # the other direction: our writer, the reference's loader, zero further steps -> the same state comes back
+    mine = str(tmp_path / "mine.params")
+    pkg.checkpoint.save_params(mine, pos, vel)
+    out2 = str(tmp_path / "state2.bin")
+    r = subprocess.run([OURS, "direct", "0", "0", "0.5", out2, "verlet", "load:" + mine], capture_output=True, text=True,
+                       timeout=120)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-1000:]
+    back = np.fromfile(out2, dtype=np.float32).reshape(2, n, 4)
+    assert np.array_equal(back[0], pos) and np.array_equal(back[1][:, :3], vel[:, :3])
