@@ -898,7 +898,6 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         if (COUNT) { c_exam += __popc(__ballot_sync(FULLM, present)); c_inter += __popc(accm); }
         if (accp) lst[lcount + __popc(accm & below)] = rec;
         lcount += __popc(accm);
-        if (lcount >= 32) flush();
         const int nrej = __popc(rejm);
         if (qtop + nrej > WL_QCAP) { overflow = true; break; }
         if (rej) q[qtop + __popc(rejm & below)] = link;
@@ -921,6 +920,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
             rec = cblk[4 * (size_t)id + (lane & 3)];
             link = clink[4 * (size_t)id + (lane & 3)];
         }
+        if (lcount >= 32) flush();   // the loads just issued are in flight while the list is evaluated
         unsigned bm = __ballot_sync(FULLM, is_bucket && (lane & 3) == 0);
         while (bm) {   // depth-cap buckets: every body of the cell, summed by all lanes
             const int src = __ffs(bm) - 1;
