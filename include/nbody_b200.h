@@ -196,6 +196,21 @@ int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, const float* a
 int nb_stats(nb_context* ctx, const float* pos, const float* vel, int n, int target_begin, int target_count, int dim,
              double out[3], void* stream);
 
+/* ---- device-side initial conditions (callers of the path) -------------------- */
+
+/* UniformEllipsoid (src/InitialConditions.cu:111-144) with a counter-based generator (splitmix64 of seed, stream,
+ * index: the same bodies on any host, any GPU, any shard): bodies [offset, offset+count) of `pos` get
+ * centre + radius*lambda*(cos phi, sin phi), phi ~ U[0,2pi), lambda ~ U[0.02,1), z = 0 or U[-h,h], mass `mass`;
+ * body `offset` becomes the central mass (DiskModel, :157) unless central_mass < 0; `vel` (slice-local, may be NULL)
+ * is set to the bulk velocity. */
+int nb_ic_uniform_ellipsoid(nb_context* ctx, float* pos, float* vel, int offset, int count, uint64_t seed, double cx, double cy,
+                            double rx, double ry, double z_half_height, float mass, float central_mass, float vx, float vy,
+                            void* stream);
+/* The velocity loop of DiskModel::initialize (src/InitialConditions.cu:169-192) after one force evaluation:
+ * v = sqrt(|a| r), tangential, in the reference's FP32 arithmetic; acc and vel are slice-local float4[count]. */
+int nb_ic_disk_velocities(nb_context* ctx, const float* pos, const float* acc, float* vel, int begin, int count, float cx, float cy,
+                          int dim, float bulk_vx, float bulk_vy, void* stream);
+
 /* ---- calibration --------------------------------------------------------------------------------- */
 
 /* Measures this GPU's FP32 roofline denominators with register-resident microbenchmarks:

@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "nb_direct_last_launch",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
-    "nb_integrate_substep", "nb_stats",
+    "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_disk_velocities",
 ]
 
 
@@ -65,6 +65,9 @@ def lib():
         L.nb_calibrate.argtypes = [vp, C.POINTER(C.c_double)]
         L.nb_verlet_dkd_drift.argtypes = [vp, vp, vp, i, i, f, vp]
         L.nb_verlet_dkd_kick_drift.argtypes = [vp, vp, vp, vp, i, i, f, vp]
+        d = C.c_double
+        L.nb_ic_uniform_ellipsoid.argtypes = [vp, vp, vp, i, i, C.c_uint64, d, d, d, d, d, f, f, f, f, vp]
+        L.nb_ic_disk_velocities.argtypes = [vp, vp, vp, vp, i, i, f, f, i, f, f, vp]
         L.nb_stats.argtypes = [vp, vp, vp, i, i, i, i, C.POINTER(C.c_double), vp]
         L.nb_integrate_substep.argtypes = [vp, vp, vp, vp, vp, i, i, f, i, C.c_double, i, C.c_double, vp]
         _lib = L
@@ -213,6 +216,20 @@ class Engine:
         self._check(lib().nb_stats(self._h, pos.data_ptr(), vel.data_ptr(), n, target_begin, cnt, dim, out,
                                    _stream_ptr(stream)), "nb_stats")
         return out[0], out[1], out[2]
+
+    # -- device-side initial conditions ---------------------------------------------------------------------
+    def ic_uniform_ellipsoid(self, pos, offset, count, seed=1, centre=(0.0, 0.0), radius=(30000.0, 30000.0),
+                             z_half_height=0.0, mass=70000.0, central_mass=10000.0, vel=None, bulk_velocity=(0.0, 0.0),
+                             stream=None):
+        self._check(lib().nb_ic_uniform_ellipsoid(self._h, pos.data_ptr(), vel.data_ptr() if vel is not None else None,
+                                                  offset, count, seed, centre[0], centre[1], radius[0], radius[1],
+                                                  z_half_height, mass, central_mass, bulk_velocity[0], bulk_velocity[1],
+                                                  _stream_ptr(stream)), "nb_ic_uniform_ellipsoid")
+
+    def ic_disk_velocities(self, pos, acc, vel, begin, count, centre=(0.0, 0.0), dim=2, bulk_velocity=(0.0, 0.0), stream=None):
+        self._check(lib().nb_ic_disk_velocities(self._h, pos.data_ptr(), acc.data_ptr(), vel.data_ptr(), begin, count,
+                                                centre[0], centre[1], dim, bulk_velocity[0], bulk_velocity[1],
+                                                _stream_ptr(stream)), "nb_ic_disk_velocities")
 
     def calibrate(self):
         out = (C.c_double * 4)()

@@ -151,3 +151,32 @@ def test_simulation_stats_match_the_reference_formulae(engine, pkg):
         for a, b in ((0, 1), (1, 1300), (1300, n)):
             parts += np.array(engine.stats(dpos, dvel[a:b].contiguous(), dim, a, b - a))
         assert np.allclose(parts[:2], want[:2], rtol=rt) and np.isclose(parts[2], want[2], rtol=1e-12)
+
+
+def test_device_initial_conditions_match_the_host_generators(engine, pkg):
+    """nb_ic_uniform_ellipsoid / nb_ic_disk_velocities against ics.uniform_disk / ics.disk_velocities (same
+    counter-based generator): positions equal up to one FP32 ulp where the device's and the host's double cos/sin
+    differ in the last bit, velocities (pure FP32 arithmetic, IEEE on both sides) bit for bit."""
+    import torch
+    n = 200000
+    for zh in (0.0, 3000.0):
+        host = pkg.ics.uniform_disk(n, seed=5, z_half_height=zh)
+        pos = torch.zeros(n + 10, 4, device="cuda")
+        engine.ic_uniform_ellipsoid(pos, 10, n, seed=5, z_half_height=zh)
+        torch.cuda.synchronize()
+        dev = pos.cpu().numpy()
+        assert np.all(dev[:10] == 0)
+        d = dev[10:]
+        assert np.array_equal(d[:, 2:], host[:, 2:])
+        ulp = np.spacing(np.abs(host[:, :2]).astype(np.float32))
+        assert np.all(np.abs(d[:, :2] - host[:, :2]) <= ulp) and np.mean(d[:, :2] == host[:, :2]) > 0.9999
+    # velocities from a force evaluation, as DiskModel does
+    host = pkg.ics.uniform_disk(n, seed=5)
+    dpos = torch.from_numpy(host).cuda()
+    acc = torch.zeros(n, 4, device="cuda")
+    engine.bh_accel(dpos, acc, 0.5, EPS)
+    vel = torch.zeros(n, 4, device="cuda")
+    engine.ic_disk_velocities(dpos, acc, vel, 0, n)
+    torch.cuda.synchronize()
+    want = pkg.ics.disk_velocities(host, acc.cpu().numpy())
+    assert np.array_equal(vel.cpu().numpy(), want)
