@@ -145,6 +145,26 @@ int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* 
  * in the tree, status flags (bit 0 = stack overflow). */
 int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]);
 
+/* ---- Barnes-Hut in 3D (octree) -------------------------------------------------------------------- */
+
+/* NO COUNTERPART IN THE REFERENCE, which runs Barnes-Hut in R2 only (src/ComputeMethods.cpp:35-38; the adapter keeps
+ * that downgrade).  The 2D pipeline one dimension up, same rules: fmaf-padded box, 21 levels of '>=' bisection packed
+ * in a 63-bit key, one stable radix sort, lock-free octree, unanimous-vote walk over 32 key-consecutive targets with
+ * the parent-width criterion, Newtonian force law of direct3DCompute.  pos/acc: device float4[n]; acc = (ax, ay, az, 0).
+ * Only NB_BH_COUNT_WALK is honoured in `flags`.  Checked against the CPU octree of oracle/ and the FP64 direct sum. */
+int nb_bh3d_accel(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening, int flags,
+                  void* stream);
+int nb_bh3d_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening, int flags,
+                         int group_begin, int group_count, void* stream);
+/* bounds6 = padded (minX, minY, minZ, maxX, maxY, maxZ); tree_keys in body order; sorted_idx = the sort permutation. */
+int nb_bh3d_stages_host(nb_context* ctx, const float* pos, int n, float* bounds6, uint64_t* tree_keys,
+                        int32_t* sorted_idx);
+/* As nb_bh_export_tree, with a third centre-of-mass coordinate; prefix digits are (x>=midX)+2(y>=midY)+4(z>=midZ),
+ * three bits per level from bit 62 down. */
+int nb_bh3d_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* level, int32_t* count, double* mass,
+                        double* cx, double* cy, double* cz);
+int nb_bh3d_last_counters(nb_context* ctx, int64_t counters[6]);
+
 /* ---- Leapfrog kick/drift on a target slice (callers of the path) ------------ */
 
 /* The two kernels Verlet_DKD::integrate launches around computeAcceleration (src/IntegrationMethods.cu:

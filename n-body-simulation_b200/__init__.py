@@ -27,6 +27,7 @@ ABI_SYMBOLS = [
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
     "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_disk_velocities",
+    "nb_bh3d_accel", "nb_bh3d_accel_groups", "nb_bh3d_stages_host", "nb_bh3d_export_tree", "nb_bh3d_last_counters",
 ]
 
 
@@ -62,6 +63,11 @@ def lib():
         L.nb_bh_stages_host.argtypes = [vp, vp, i, i, vp, vp, vp, vp]
         L.nb_bh_export_tree.argtypes = [vp, C.POINTER(i), vp, vp, vp, vp, vp, vp]
         L.nb_bh_last_counters.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.nb_bh3d_accel.argtypes = [vp, vp, vp, i, f, f, i, vp]
+        L.nb_bh3d_accel_groups.argtypes = [vp, vp, vp, i, f, f, i, i, i, vp]
+        L.nb_bh3d_stages_host.argtypes = [vp, vp, i, vp, vp, vp]
+        L.nb_bh3d_export_tree.argtypes = [vp, C.POINTER(i), vp, vp, vp, vp, vp, vp, vp]
+        L.nb_bh3d_last_counters.argtypes = [vp, C.POINTER(C.c_int64)]
         L.nb_calibrate.argtypes = [vp, C.POINTER(C.c_double)]
         L.nb_verlet_dkd_drift.argtypes = [vp, vp, vp, i, i, f, vp]
         L.nb_verlet_dkd_kick_drift.argtypes = [vp, vp, vp, vp, i, i, f, vp]
@@ -230,6 +236,48 @@ class Engine:
         self._check(lib().nb_ic_disk_velocities(self._h, pos.data_ptr(), acc.data_ptr(), vel.data_ptr(), begin, count,
                                                 centre[0], centre[1], dim, bulk_velocity[0], bulk_velocity[1],
                                                 _stream_ptr(stream)), "nb_ic_disk_velocities")
+
+    # -- Barnes-Hut in 3D (octree; no reference counterpart) --------------------------------------------------
+    def bh3d_accel(self, pos, acc, theta, softening, flags=0, stream=None):
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(acc, n)
+        self._check(lib().nb_bh3d_accel(self._h, pos.data_ptr(), acc.data_ptr(), n, theta, softening, flags,
+                                        _stream_ptr(stream)), "nb_bh3d_accel")
+
+    def bh3d_accel_groups(self, pos, acc, theta, softening, group_begin, group_count, flags=0, stream=None):
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(acc, n)
+        self._check(lib().nb_bh3d_accel_groups(self._h, pos.data_ptr(), acc.data_ptr(), n, theta, softening, flags,
+                                               group_begin, group_count, _stream_ptr(stream)), "nb_bh3d_accel_groups")
+
+    def bh3d_stages(self, pos):
+        n = pos.shape[0]
+        _check_tensor(pos, n)
+        bounds = np.zeros(6, np.float32)
+        tkeys = np.zeros(n, np.uint64)
+        sidx = np.zeros(n, np.int32)
+        self._check(lib().nb_bh3d_stages_host(self._h, pos.data_ptr(), n, bounds.ctypes.data, tkeys.ctypes.data,
+                                              sidx.ctypes.data), "nb_bh3d_stages_host")
+        return dict(bounds=bounds, tree_keys=tkeys, sorted_idx=sidx)
+
+    def bh3d_export_tree(self):
+        k = C.c_int()
+        self._check(lib().nb_bh3d_export_tree(self._h, C.byref(k), None, None, None, None, None, None, None),
+                    "nb_bh3d_export_tree")
+        k = k.value
+        out = dict(prefix=np.zeros(k, np.uint64), level=np.zeros(k, np.int32), count=np.zeros(k, np.int32),
+                   mass=np.zeros(k, np.float64), cx=np.zeros(k, np.float64), cy=np.zeros(k, np.float64),
+                   cz=np.zeros(k, np.float64))
+        kk = C.c_int(k)
+        self._check(lib().nb_bh3d_export_tree(self._h, C.byref(kk), out["prefix"].ctypes.data, out["level"].ctypes.data,
+                                              out["count"].ctypes.data, out["mass"].ctypes.data, out["cx"].ctypes.data,
+                                              out["cy"].ctypes.data, out["cz"].ctypes.data), "nb_bh3d_export_tree")
+        return out
+
+    def bh3d_last_counters(self):
+        c = (C.c_int64 * 6)()
+        self._check(lib().nb_bh3d_last_counters(self._h, c), "nb_bh3d_last_counters")
+        return dict(opened=c[0], examined=c[1], interactions=c[2], max_stack=c[3], nodes=c[4], status=c[5])
 
     def calibrate(self):
         out = (C.c_double * 4)()

@@ -6,6 +6,7 @@ char g_nb_create_error[512] = {0};
 int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
                      int dim, float softening, int flags, cudaStream_t stream);  // direct.cu
 void nb_bh_destroy(nb_context* ctx);                                              // bh.cu
+void nb_bh3_destroy(nb_context* ctx);                                             // bh3d.cu
 
 extern "C" {
 
@@ -42,6 +43,7 @@ int nb_destroy(nb_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     nb_bh_destroy(ctx);
+    nb_bh3_destroy(ctx);
     if (ctx->partial) cudaFree(ctx->partial);
     if (ctx->tile_flags) cudaFree(ctx->tile_flags);
     if (ctx->stats) cudaFree(ctx->stats);

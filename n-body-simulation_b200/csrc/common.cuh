@@ -8,7 +8,8 @@
 
 #include "../../include/nbody_b200.h"
 
-struct nb_bh_state;  // bh.cu
+struct nb_bh_state;   // bh.cu
+struct nb_bh3_state;  // bh3d.cu
 
 struct nb_context {
     int device = 0;
@@ -29,6 +30,7 @@ struct nb_context {
     int last_jsplit = 0, last_blocks = 0, last_launches = 0;
 
     nb_bh_state* bh = nullptr;
+    nb_bh3_state* bh3 = nullptr;
     cudaStream_t host_stream = nullptr;  // used by the *_host entry points
 };
 

@@ -693,3 +693,281 @@ ORACLE_API int oracle_bh_accel(const float *pos, int n, float theta, float eps, 
     free(keys); free(skeys); free(sidx);
     return k;
 }
+
+/* ------------------------------------------------------------------------------------------ */
+/* Barnes-Hut in 3D (octree).  NO REFERENCE COUNTERPART: the reference forces Barnes-Hut to R2 */
+/* (src/ComputeMethods.cpp:35-38).  These functions extend the restated 2D rules one dimension */
+/* up -- same padding, same '>=' bisection, same bucket-1 region tree, same unanimous-vote     */
+/* parent-width criterion, the 3D force law of src/DirectComputeKernels.cu:60-68 -- and serve  */
+/* as the checker of the 3D CUDA path (parity unpinned by the reference; accuracy is checked   */
+/* against the FP64 direct sum).  Keys: 21 levels x 3 bits = 63 bits, first level in 62:60.    */
+/* ------------------------------------------------------------------------------------------ */
+#define ORACLE3_MAX_LEVEL 21
+
+ORACLE_API void oracle_bh3_bounds(const float *pos, int n, float *b6)
+{
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = 0; i < n; i++)
+        for (int k = 0; k < 3; k++) {
+            mn[k] = fminf(mn[k], pos[4 * (size_t)i + k]);
+            mx[k] = fmaxf(mx[k], pos[4 * (size_t)i + k]);
+        }
+    for (int k = 0; k < 3; k++) {
+        b6[k] = fmaf(fabsf(mn[k]), -0.001f, mn[k]);
+        b6[3 + k] = fmaf(fabsf(mx[k]), 0.001f, mx[k]);
+    }
+}
+
+static inline int path3_of(const float *p, float *lo, float *hi)
+{
+    int path = 0;
+    for (int k = 0; k < 3; k++) {
+        float mid = (hi[k] + lo[k]) * 0.5f;
+        if (p[k] >= mid) { lo[k] = mid; path += 1 << k; } else { hi[k] = mid; }
+    }
+    return path;
+}
+
+ORACLE_API void oracle_bh3_tree_keys(const float *pos, int n, const float *b6, uint64_t *keys)
+{
+    for (int b = 0; b < n; b++) {
+        float lo[3] = {b6[0], b6[1], b6[2]}, hi[3] = {b6[3], b6[4], b6[5]};
+        uint64_t key = 0;
+        for (int lev = 0; lev < ORACLE3_MAX_LEVEL; lev++)
+            key |= (uint64_t)path3_of(pos + 4 * (size_t)b, lo, hi) << (60 - 3 * lev);
+        keys[b] = key;
+    }
+}
+
+typedef struct {
+    int child[8];
+    int level, count;
+    uint64_t prefix;
+    double m, mx, my, mz;
+    int bucket_head;
+} o3node;
+
+typedef struct {
+    o3node *nodes;
+    int n_nodes, cap;
+    int *bucket_next;
+    int n;
+    float b6[6];
+    const float *pos;
+} o3tree;
+
+static int o3_new(o3tree *t, int level, uint64_t prefix)
+{
+    if (t->n_nodes == t->cap) {
+        t->cap = t->cap * 2 + 16;
+        t->nodes = (o3node *)realloc(t->nodes, sizeof(o3node) * (size_t)t->cap);
+    }
+    o3node *nd = &t->nodes[t->n_nodes];
+    for (int k = 0; k < 8; k++) nd->child[k] = -1;
+    nd->level = level; nd->count = 0; nd->prefix = prefix;
+    nd->m = nd->mx = nd->my = nd->mz = 0.0;
+    nd->bucket_head = -1;
+    return t->n_nodes++;
+}
+
+static void o3_insert(o3tree *t, int body)
+{
+    const float *p = t->pos + 4 * (size_t)body;
+    double w = p[3];
+    float lo[3] = {t->b6[0], t->b6[1], t->b6[2]}, hi[3] = {t->b6[3], t->b6[4], t->b6[5]};
+    int node = 0;
+    for (;;) {
+        o3node *nd = &t->nodes[node];
+        nd->m += w; nd->mx += w * p[0]; nd->my += w * p[1]; nd->mz += w * p[2]; nd->count++;
+        if (nd->level == ORACLE3_MAX_LEVEL) {
+            t->bucket_next[body] = nd->bucket_head;
+            nd->bucket_head = body;
+            return;
+        }
+        float clo[3] = {lo[0], lo[1], lo[2]}, chi[3] = {hi[0], hi[1], hi[2]};
+        int path = path3_of(p, clo, chi);
+        int slot = nd->child[path];
+        int clevel = nd->level + 1;
+        uint64_t cprefix = nd->prefix | ((uint64_t)path << (60 - 3 * nd->level));
+        if (IS_NODE(slot)) {
+            node = NODE_ID(slot);
+            memcpy(lo, clo, sizeof(lo)); memcpy(hi, chi, sizeof(hi));
+            continue;
+        }
+        if (slot == -1) { nd->child[path] = body; return; }
+        int resident = slot;
+        int nn = o3_new(t, clevel, cprefix);
+        nd = &t->nodes[node];
+        nd->child[path] = NODE_REF(nn);
+        o3node *c = &t->nodes[nn];
+        const float *rp = t->pos + 4 * (size_t)resident;
+        double rw = rp[3];
+        c->m += rw; c->mx += rw * rp[0]; c->my += rw * rp[1]; c->mz += rw * rp[2]; c->count++;
+        if (clevel == ORACLE3_MAX_LEVEL) {
+            t->bucket_next[resident] = c->bucket_head;
+            c->bucket_head = resident;
+        } else {
+            float a[3] = {clo[0], clo[1], clo[2]}, b[3] = {chi[0], chi[1], chi[2]};
+            c->child[path3_of(rp, a, b)] = resident;
+        }
+        node = nn;
+        memcpy(lo, clo, sizeof(lo)); memcpy(hi, chi, sizeof(hi));
+    }
+}
+
+ORACLE_API void *oracle_bh3_tree_build(const float *pos, int n, const float *b6, const int32_t *order)
+{
+    o3tree *t = (o3tree *)calloc(1, sizeof(o3tree));
+    t->pos = pos; t->n = n;
+    memcpy(t->b6, b6, sizeof(float) * 6);
+    t->bucket_next = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) t->bucket_next[i] = -1;
+    o3_new(t, 0, 0);
+    for (int i = 0; i < n; i++) o3_insert(t, order ? order[i] : i);
+    return t;
+}
+
+ORACLE_API void oracle_bh3_tree_free(void *h)
+{
+    o3tree *t = (o3tree *)h;
+    if (!t) return;
+    free(t->nodes); free(t->bucket_next); free(t);
+}
+
+typedef struct { uint64_t prefix; int level, count; double m, cx, cy, cz; } o3cell;
+static int o3cell_cmp(const void *a, const void *b)
+{
+    const o3cell *p = (const o3cell *)a, *q = (const o3cell *)b;
+    if (p->prefix != q->prefix) return p->prefix < q->prefix ? -1 : 1;
+    return p->level - q->level;
+}
+
+ORACLE_API int oracle_bh3_tree_canonical(void *h, uint64_t *prefix, int32_t *level, int32_t *count, double *mass,
+                                         double *cx, double *cy, double *cz)
+{
+    o3tree *t = (o3tree *)h;
+    int k = 0;
+    for (int i = 0; i < t->n_nodes; i++) if (t->nodes[i].count >= 2) k++;
+    if (!prefix) return k;
+    o3cell *cells = (o3cell *)malloc(sizeof(o3cell) * (size_t)(k > 0 ? k : 1));
+    k = 0;
+    for (int i = 0; i < t->n_nodes; i++) {
+        o3node *nd = &t->nodes[i];
+        if (nd->count < 2) continue;
+        cells[k].prefix = nd->prefix; cells[k].level = nd->level; cells[k].count = nd->count; cells[k].m = nd->m;
+        cells[k].cx = nd->m > 0 ? nd->mx / nd->m : 0.0;
+        cells[k].cy = nd->m > 0 ? nd->my / nd->m : 0.0;
+        cells[k].cz = nd->m > 0 ? nd->mz / nd->m : 0.0;
+        k++;
+    }
+    qsort(cells, (size_t)k, sizeof(o3cell), o3cell_cmp);
+    for (int i = 0; i < k; i++) {
+        prefix[i] = cells[i].prefix; level[i] = cells[i].level; count[i] = cells[i].count; mass[i] = cells[i].m;
+        cx[i] = cells[i].cx; cy[i] = cells[i].cy; cz[i] = cells[i].cz;
+    }
+    free(cells);
+    return k;
+}
+
+/* Walk: the rules of oracle_bh_walk with a third coordinate and the Newtonian law
+ * k = inv*inv*inv*m, inv = 1/sqrt(S + |d|^2) (src/DirectComputeKernels.cu:64-67). */
+ORACLE_API void oracle_bh3_walk(void *h, const int32_t *sorted_idx, int g0, int g1, float theta, float eps, float *acc,
+                                int64_t *counters, int threads)
+{
+    o3tree *t = (o3tree *)h;
+    const float *pos = t->pos;
+    const int n = t->n;
+    const float dim_size = fmaxf(fmaxf(t->b6[3] - t->b6[0], t->b6[4] - t->b6[1]), t->b6[5] - t->b6[2]);
+    float s0 = dim_size / theta;
+    s0 *= s0;
+    int64_t c_open = 0, c_exam = 0, c_inter = 0, c_depth = 0;
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+#endif
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads) reduction(+ : c_open, c_exam, c_inter) reduction(max : c_depth)
+    for (int g = g0; g < g1; g++) {
+        int base = g * 32;
+        int lanes = n - base < 32 ? n - base : 32;
+        if (lanes <= 0) continue;
+        float x[32], y[32], z[32], ax[32], ay[32], az[32];
+        for (int l = 0; l < lanes; l++) {
+            int b = sorted_idx[base + l];
+            x[l] = pos[4 * (size_t)b]; y[l] = pos[4 * (size_t)b + 1]; z[l] = pos[4 * (size_t)b + 2];
+            ax[l] = ay[l] = az[l] = 0.f;
+        }
+        int st_node[8 * ORACLE3_MAX_LEVEL + 16];
+        float st_size[8 * ORACLE3_MAX_LEVEL + 16];
+        int top = -1;
+        for (int i = 0; i < 8; i++) {
+            int c = t->nodes[0].child[i];
+            if (c == -1) continue;
+            top++; st_node[top] = c; st_size[top] = s0;
+        }
+#define O3_ADD(CX, CY, CZ, CM)                                                           \
+        for (int l = 0; l < lanes; l++) {                                                \
+            float dx = (CX) - x[l], dy = (CY) - y[l], dz = (CZ) - z[l];                  \
+            float r = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps)));                     \
+            float inv = 1.0f / sqrtf(r);                                                 \
+            float k = inv * inv * inv * (CM);                                            \
+            ax[l] = fmaf(k, dx, ax[l]); ay[l] = fmaf(k, dy, ay[l]); az[l] = fmaf(k, dz, az[l]); \
+        }
+        while (top >= 0) {
+            if (top + 1 > c_depth) c_depth = top + 1;
+            int ref = st_node[top];
+            float size = st_size[top] * 0.25f;
+            if (!IS_NODE(ref)) {   /* a body directly under the root */
+                O3_ADD(pos[4 * (size_t)ref], pos[4 * (size_t)ref + 1], pos[4 * (size_t)ref + 2], pos[4 * (size_t)ref + 3]);
+                c_inter += lanes;
+                top--;
+                continue;
+            }
+            o3node *nd = &t->nodes[NODE_ID(ref)];
+            c_open++;
+            if (nd->level == ORACLE3_MAX_LEVEL) {
+                for (int b = nd->bucket_head; b >= 0; b = t->bucket_next[b]) {
+                    O3_ADD(pos[4 * (size_t)b], pos[4 * (size_t)b + 1], pos[4 * (size_t)b + 2], pos[4 * (size_t)b + 3]);
+                    c_inter += lanes; c_exam++;
+                }
+                top--;
+                continue;
+            }
+            for (int i = 0; i < 8; i++) {
+                int c = nd->child[i];
+                if (c == -1) continue;
+                c_exam++;
+                float cx, cy, cz, cm;
+                int is_body = !IS_NODE(c);
+                if (is_body) {
+                    cx = pos[4 * (size_t)c]; cy = pos[4 * (size_t)c + 1]; cz = pos[4 * (size_t)c + 2]; cm = pos[4 * (size_t)c + 3];
+                } else {
+                    o3node *cn = &t->nodes[NODE_ID(c)];
+                    if (cn->m > 0) { cx = (float)(cn->mx / cn->m); cy = (float)(cn->my / cn->m); cz = (float)(cn->mz / cn->m); }
+                    else { cx = cy = cz = 0.f; }
+                    cm = (float)cn->m;
+                }
+                int accept = 1;
+                for (int l = 0; l < lanes; l++) {
+                    float dx = cx - x[l], dy = cy - y[l], dz = cz - z[l];
+                    float r = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, eps)));
+                    if (!(size <= r)) accept = 0;
+                }
+                if (is_body || accept) {
+                    O3_ADD(cx, cy, cz, cm);
+                    c_inter += lanes;
+                } else {
+                    st_node[top] = c; st_size[top] = size; top++;
+                }
+            }
+            top--;
+        }
+#undef O3_ADD
+        for (int l = 0; l < lanes; l++) {
+            int b = sorted_idx[base + l];
+            acc[4 * (size_t)b + 0] = ax[l]; acc[4 * (size_t)b + 1] = ay[l]; acc[4 * (size_t)b + 2] = az[l]; acc[4 * (size_t)b + 3] = 0.f;
+        }
+    }
+    if (counters) {
+        counters[0] += c_open; counters[1] += c_exam; counters[2] += c_inter;
+        if (c_depth > counters[3]) counters[3] = c_depth;
+    }
+}

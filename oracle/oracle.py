@@ -48,6 +48,14 @@ def lib():
         L.oracle_bh_walk.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_float, C.c_float, f32p, i64p, C.c_int]
         L.oracle_bh_accel.argtypes = [f32p, C.c_int, C.c_float, C.c_float, C.c_int, f32p, f32p, u32p, i32p, i64p, C.c_int]
         L.oracle_bh_accel.restype = C.c_int
+        L.oracle_bh3_bounds.argtypes = [f32p, C.c_int, f32p]
+        L.oracle_bh3_tree_keys.argtypes = [f32p, C.c_int, f32p, u64p]
+        L.oracle_bh3_tree_build.argtypes = [f32p, C.c_int, f32p, i32p]
+        L.oracle_bh3_tree_build.restype = C.c_void_p
+        L.oracle_bh3_tree_free.argtypes = [C.c_void_p]
+        L.oracle_bh3_tree_canonical.argtypes = [C.c_void_p, u64p, i32p, i32p, f64p, f64p, f64p, f64p]
+        L.oracle_bh3_tree_canonical.restype = C.c_int
+        L.oracle_bh3_walk.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_float, C.c_float, f32p, i64p, C.c_int]
         _LIB = L
     return _LIB
 
@@ -179,3 +187,69 @@ def bh_accel(pos, theta, eps, prebuilt=False, threads=0):
     return dict(acc=acc, bounds=bounds, keys=keys, sorted_idx=sidx, nodes=k,
                 counters=dict(opened=int(counters[0]), examined=int(counters[1]),
                               interactions=int(counters[2]), max_stack=int(counters[3])))
+
+
+# ---- 3D (octree) extension: no reference counterpart, see nbody_oracle.c -------------------------------------
+
+def bh3_bounds(pos):
+    pos = _pos(pos)
+    b = np.zeros(6, np.float32)
+    lib().oracle_bh3_bounds(_p(pos, C.c_float), pos.shape[0], _p(b, C.c_float))
+    return b
+
+
+def bh3_tree_keys(pos, bounds):
+    pos = _pos(pos)
+    b = np.ascontiguousarray(bounds, np.float32)
+    k = np.zeros(pos.shape[0], np.uint64)
+    lib().oracle_bh3_tree_keys(_p(pos, C.c_float), pos.shape[0], _p(b, C.c_float), _p(k, C.c_uint64))
+    return k
+
+
+class Tree3:
+    """Oracle octree (sequential insertion, 21-level cap)."""
+
+    def __init__(self, pos, bounds, order=None):
+        self.pos = _pos(pos)
+        self.bounds = np.ascontiguousarray(bounds, np.float32)
+        self.n = self.pos.shape[0]
+        o = None if order is None else np.ascontiguousarray(order, np.int32)
+        self._h = lib().oracle_bh3_tree_build(_p(self.pos, C.c_float), self.n, _p(self.bounds, C.c_float),
+                                              None if o is None else _p(o, C.c_int32))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().oracle_bh3_tree_free(self._h)
+            self._h = None
+
+    def canonical(self):
+        k = lib().oracle_bh3_tree_canonical(self._h, None, None, None, None, None, None, None)
+        out = dict(prefix=np.zeros(k, np.uint64), level=np.zeros(k, np.int32), count=np.zeros(k, np.int32),
+                   mass=np.zeros(k, np.float64), cx=np.zeros(k, np.float64), cy=np.zeros(k, np.float64),
+                   cz=np.zeros(k, np.float64))
+        lib().oracle_bh3_tree_canonical(self._h, _p(out["prefix"], C.c_uint64), _p(out["level"], C.c_int32),
+                                        _p(out["count"], C.c_int32), _p(out["mass"], C.c_double),
+                                        _p(out["cx"], C.c_double), _p(out["cy"], C.c_double), _p(out["cz"], C.c_double))
+        return out
+
+    def walk(self, sorted_idx, theta, eps, g0=0, g1=None, threads=0):
+        sidx = np.ascontiguousarray(sorted_idx, np.int32)
+        groups = (self.n + 31) // 32
+        g1 = groups if g1 is None else g1
+        acc = np.zeros((self.n, 4), np.float32)
+        counters = np.zeros(4, np.int64)
+        lib().oracle_bh3_walk(self._h, _p(sidx, C.c_int32), g0, g1, theta, eps, _p(acc, C.c_float),
+                              _p(counters, C.c_int64), threads)
+        return acc, dict(opened=int(counters[0]), examined=int(counters[1]), interactions=int(counters[2]),
+                         max_stack=int(counters[3]))
+
+
+def bh3_accel(pos, theta, eps, threads=0):
+    """bounds -> 63-bit keys -> stable sort -> octree -> walk (groups of 32 in key order)."""
+    pos = _pos(pos)
+    b = bh3_bounds(pos)
+    k = bh3_tree_keys(pos, b)
+    sk, si = sort_pairs(k)
+    t = Tree3(pos, b, si)
+    acc, cnt = t.walk(si, theta, eps, threads=threads)
+    return dict(acc=acc, bounds=b, keys=k, sorted_idx=si, counters=cnt, tree=t)

@@ -182,3 +182,20 @@ def test_ics_are_reproducible(pkg):
     r = np.hypot(a[1:, 0], a[1:, 1])
     assert r.min() >= 0.02 * 30000 * 0.999 and r.max() <= 30000
     assert not np.array_equal(a, pkg.ics.uniform_disk(1000, seed=2))
+
+
+def test_oracle_octree_converges_to_direct_sum(oracle, pkg):
+    """The 3D extension of the oracle (no reference counterpart): theta -> 0 equals the 3D direct sum, theta = 0.5
+    stays within a sub-percent error distribution, keys sort like the tree's cells."""
+    pos = pkg.ics.uniform_disk(4096, seed=81, z_half_height=3000.0)
+    d = oracle.direct_f64(pos, 3, EPS)
+    r = oracle.bh3_accel(pos, 1e-4, EPS)
+    e = np.linalg.norm(r["acc"][:, :3] - d, axis=1) / np.linalg.norm(d, axis=1)
+    assert e.max() < 5e-5
+    r = oracle.bh3_accel(pos, 0.5, EPS)
+    e = np.linalg.norm(r["acc"][:, :3] - d, axis=1) / np.linalg.norm(d, axis=1)
+    assert np.median(e) < 2e-3 and e.max() < 0.1
+    assert r["counters"]["interactions"] < 0.8 * 4096 * 4096     # theta/2 opening angle in 3D: most of a small system is near field
+    c = r["tree"].canonical()
+    assert c["level"][0] == 0 and c["count"][0] == 4096 and c["level"].max() <= 21
+    assert np.all(r["keys"] >> np.uint64(63) == 0)
