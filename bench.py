@@ -400,6 +400,22 @@ def main():
         except pkg.NbodyError as e:
             extra["bh"] = {"unavailable": str(e)}
 
+    # ---- Barnes-Hut in 3D (octree; beyond the reference): informative --------------------
+    if not args.skip_bh and world == 1:
+        try:
+            p3 = torch.from_numpy(pkg.ics.uniform_disk(N_BODIES, seed=1, z_half_height=3000.0)).to(dev)
+            a3 = torch.zeros(N_BODIES, 4, device=dev)
+            ms3 = timed(lambda: eng.bh3d_accel(p3, a3, THETA, EPS), 5, 3) / 5
+            eng.bh3d_accel(p3, a3, THETA, EPS, pkg.NB_BH_COUNT_WALK)
+            c3 = eng.bh3d_last_counters()
+            extra["bh3d"] = {"metric": "octree BH steps/s (N=1M thick disc, theta=0.5)", "value": 1e3 / ms3, "unit": "steps/s",
+                             "ms_per_step": ms3, "counters": c3,
+                             "lane_interactions_per_s": c3["interactions"] / (ms3 * 1e-3),
+                             "note": "no reference counterpart (the reference forces Barnes-Hut to R2)"}
+            del p3, a3
+        except pkg.NbodyError as e:
+            extra["bh3d"] = {"unavailable": str(e)}
+
     # ---- host baseline (rank 0, N=1 only) ----------------------------------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.skip_cpu:
