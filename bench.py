@@ -117,7 +117,40 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def ref_bh_worker(out_path):
+    """Child process of the bench: the reference's own Barnes-Hut kernels at the benchmark size, four evaluations."""
+    import ctypes as C
+    import torch
+    pkg = graft.load_package()
+    nb = N_BODIES
+    ref = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so"))
+    vp = C.c_void_p
+    ref.ref_barnes_hut.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_float]
+    dev = torch.device("cuda", 0)
+    m = 3 * nb
+    rp = torch.zeros(m, 4, device=dev)
+    rp[:nb] = torch.from_numpy(pkg.ics.uniform_disk(nb, seed=1)).to(dev)
+    ra = torch.zeros(nb, 4, device=dev)
+    fmax = float(np.finfo(np.float32).max)
+    rb = torch.tensor([fmax, fmax, -fmax, -fmax], device=dev)
+    ri = torch.zeros(1, dtype=torch.int32, device=dev)
+    rn = torch.zeros(4 * m, dtype=torch.int32, device=dev)
+    rs = torch.zeros(nb, dtype=torch.int32, device=dev)
+    rk = torch.zeros(nb, dtype=torch.int32, device=dev)
+    tms = []
+    for _ in range(4):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ref.ref_barnes_hut(rp.data_ptr(), ra.data_ptr(), rb.data_ptr(), ri.data_ptr(), rn.data_ptr(), rs.data_ptr(),
+                           rk.data_ptr(), nb, m, THETA, EPS)   # synchronises itself
+        tms.append((time.perf_counter() - t0) * 1e3)
+    np.save(out_path, ra[:, :2].cpu().numpy())
+    print(json.dumps({"ms": tms}), flush=True)
+
+
 def main():
+    if len(sys.argv) == 3 and sys.argv[1] == "--ref-bh-worker":
+        return ref_bh_worker(sys.argv[2])
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -363,27 +396,24 @@ def main():
                                               "theta_error_median": float(np.median(oerr))}
                     so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
                     if os.path.exists(so) and not args.skip_refcuda:
-                        import ctypes as C
-                        ref = C.CDLL(so)
-                        vp = C.c_void_p
-                        ref.ref_barnes_hut.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_float]
-                        m = 3 * nb
-                        rp = torch.zeros(m, 4, device=dev)
-                        rp[:nb] = p2
+                        # the reference's lock-based tree build can stall on sm_100 (spin on a slot with a divergent
+                        # __syncthreads, src/BarnesHutKernels.cu:296-363): run it in a child process with a time limit
+                        import tempfile
+                        tmp = tempfile.mkdtemp()
+                        ref_out = os.path.join(tmp, "ref_acc.npy")
+                        try:
+                            cp = subprocess.run([sys.executable, os.path.abspath(__file__), "--ref-bh-worker", ref_out],
+                                                capture_output=True, text=True, timeout=120)
+                            tms = json.loads(cp.stdout.strip().splitlines()[-1])["ms"] if cp.returncode == 0 else None
+                        except (subprocess.TimeoutExpired, ValueError, IndexError, KeyError):
+                            tms = None
+                        if tms is None:
+                            bh["reference_cuda_bh"] = {"unavailable": "the reference's Barnes-Hut kernels did not finish within 120 s "
+                                                                      "(lock-based tree build stalled) or failed"}
+                            extra["bh"] = bh
+                            raise StopIteration
                         ra = torch.zeros(nb, 4, device=dev)
-                        fmax = float(np.finfo(np.float32).max)
-                        rb = torch.tensor([fmax, fmax, -fmax, -fmax], device=dev)
-                        ri = torch.zeros(1, dtype=torch.int32, device=dev)
-                        rn = torch.zeros(4 * m, dtype=torch.int32, device=dev)
-                        rs = torch.zeros(nb, dtype=torch.int32, device=dev)
-                        rk = torch.zeros(nb, dtype=torch.int32, device=dev)
-                        tms = []
-                        for _ in range(4):
-                            torch.cuda.synchronize()
-                            t0 = time.perf_counter()
-                            ref.ref_barnes_hut(rp.data_ptr(), ra.data_ptr(), rb.data_ptr(), ri.data_ptr(), rn.data_ptr(),
-                                               rs.data_ptr(), rk.data_ptr(), nb, m, THETA, EPS)   # synchronises itself
-                            tms.append((time.perf_counter() - t0) * 1e3)
+                        ra[:, :2] = torch.from_numpy(np.load(ref_out)).to(dev)
                         ref_ms = min(tms[1:])
                         d = (ra[:, :2] - a2[:, :2]).norm(dim=1) / ra[:, :2].norm(dim=1)
                         ref_err = None
@@ -397,6 +427,8 @@ def main():
                                                    "acc_rel_diff_p99": float(d.quantile(0.99)),
                                                    "what": "unmodified src/BarnesHutKernels.cu (sm_100), knodes=3, same box"}
             extra["bh"] = bh
+        except StopIteration:
+            pass
         except pkg.NbodyError as e:
             extra["bh"] = {"unavailable": str(e)}
 
