@@ -75,6 +75,18 @@ struct nb_bh_state {
     int last_n = 0;
     // result locations of the last sorts
     int sfc_sel = 0, tree_sel = 0;
+    // small systems are launch-bound (20 launches + 1 memset per evaluation): the whole evaluation is captured once
+    // into a CUDA graph and replayed while the call's arguments stay the same
+    struct GraphKey {
+        const float* pos; float* acc; int n, flags, group_begin, group_count, accumulate; float theta, eps;
+        bool operator==(const GraphKey& o) const {
+            return pos == o.pos && acc == o.acc && n == o.n && flags == o.flags && group_begin == o.group_begin &&
+                   group_count == o.group_count && accumulate == o.accumulate && theta == o.theta && eps == o.eps;
+        }
+    };
+    GraphKey graph_key{};
+    cudaGraphExec_t graph_exec = nullptr;
+    cudaStream_t capture_stream = nullptr;
 };
 
 namespace {
@@ -721,6 +733,10 @@ int alloc(nb_context* ctx, T** p, size_t count) {
 
 void free_state(nb_bh_state* st) {
     if (!st) return;
+    if (st->graph_exec) cudaGraphExecDestroy(st->graph_exec);
+    if (st->capture_stream) cudaStreamDestroy(st->capture_stream);
+    st->graph_exec = nullptr;
+    st->capture_stream = nullptr;
     void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
                     st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->ghist, st->clink, st->spos, st->psum, st->psum_blk,
                     st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
@@ -904,10 +920,38 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)
         return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
-    rc = run_build(ctx, pos, n, flags, 4, theta, (cudaStream_t)stream);
+    static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 262144; }();
+    const bool counting = (flags & NB_BH_COUNT_FLAG) != 0;
+    if (n > graph_max_n || n < 2 || counting) {
+        rc = run_build(ctx, pos, n, flags, 4, theta, (cudaStream_t)stream);
+        if (rc) return rc;
+        return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, counting, (cudaStream_t)stream);
+    }
+    // launch-bound sizes: replay a captured graph of the same evaluation
+    rc = ensure_state(ctx, n);   // allocation must not happen inside a capture
     if (rc) return rc;
-    return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, (flags & NB_BH_COUNT_FLAG) != 0,
-                    (cudaStream_t)stream);
+    nb_bh_state* st = ctx->bh;
+    const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
+    const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening};
+    if (!st->graph_exec || !(st->graph_key == key)) {
+        if (st->graph_exec) { cudaGraphExecDestroy(st->graph_exec); st->graph_exec = nullptr; }
+        if (!st->capture_stream) NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->capture_stream, cudaStreamNonBlocking));
+        NB_CUDA(ctx, cudaStreamBeginCapture(st->capture_stream, cudaStreamCaptureModeThreadLocal));
+        rc = run_build(ctx, pos, n, flags, 4, theta, st->capture_stream);
+        if (!rc) rc = run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, false, st->capture_stream);
+        cudaGraph_t graph = nullptr;
+        cudaError_t e = cudaStreamEndCapture(st->capture_stream, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) return nb_fail(ctx, NB_ERR_CUDA, "cudaStreamEndCapture", e);
+        e = cudaGraphInstantiate(&st->graph_exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) { st->graph_exec = nullptr; return nb_fail(ctx, NB_ERR_CUDA, "cudaGraphInstantiate", e); }
+        st->graph_key = key;
+    }
+    st->last_n = n;
+    st->bounds_valid = true;
+    NB_CUDA(ctx, cudaGraphLaunch(st->graph_exec, (cudaStream_t)stream));
+    return NB_OK;
 }
 
 int nb_bh_accel(nb_context* ctx, const float* pos, float* acc, int n, float theta, float softening, int flags,
