@@ -314,6 +314,17 @@ def main():
         except Exception as e:  # calibration is informative only
             roofline["calibrated"] = str(e)
 
+    # ---- the same workload in Space R2 (the reference's main.cu space; 2D force law m d/(eps+r^2), 14 flop) ----------
+    if dim == 3 and not args.skip_bh:
+        pos2d = torch.from_numpy(pkg.ics.uniform_disk(n, seed=1)).to(dev)
+        ms2d = timed(lambda: eng.direct_accel_slice(pos2d, begin, count, acc, 2, EPS), 2, 1) / 2
+        ach2d = float(count) * float(n) * FLOP_PER_INTERACTION[2] / (ms2d * 1e-3) / 1e12
+        extra["direct_2d"] = {"metric": "interactions/s (direct 2D, N=%d)" % n, "value": interactions / (ms2d * 1e-3),
+                              "kernel_ms": ms2d,
+                              "roofline_frac_fp32": ach2d / peak,
+                              "note": "2D is co-limited by the MUFU pipe (one rsqrt per 8 FP32 ops)"}
+        del pos2d
+
     # ---- the reference's own CUDA kernel on the same box (informative; north_star parity target) ---------
     if rank == 0 and world == 1 and not args.skip_refcuda:
         so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
