@@ -578,7 +578,9 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
                                                                   int group_begin, int group_count, float4* __restrict__ acc,
                                                                   unsigned long long* __restrict__ counters) {
     __shared__ uint32_t q_s[WL_WARPS][WL_QCAP];
-    __shared__ float4 l_s[WL_WARPS][WL_LCAP];
+    // pending accepted records, two per slot so that the evaluation runs on FP32x2: (cx0, cx1, cy0, cy1) and (m0, m1)
+    __shared__ float4 lxy_s[WL_WARPS][WL_LCAP / 2];
+    __shared__ float2 lm_s[WL_WARPS][WL_LCAP / 2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned FULLM = 0xffffffffu;
     const int g = blockIdx.x * WL_WARPS + warp;
@@ -599,8 +601,11 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         by1 = fmaxf(by1, __shfl_xor_sync(FULLM, by1, o));
     }
     float ax = 0.f, ay = 0.f;
+    uint64_t AX2 = 0ull, AY2 = 0ull;          // packed partial sums of the list evaluation (even / odd records)
+    const uint64_t X2 = pk2(x, x), Y2 = pk2(y, y), E2 = pk2(eps, eps);
     uint32_t* const q = q_s[warp];
-    float4* const lst = l_s[warp];
+    float* const lxy = reinterpret_cast<float*>(lxy_s[warp]);
+    float* const lm = reinterpret_cast<float*>(lm_s[warp]);
     int qtop = 0, lcount = 0;
     unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
     int c_depth = 0;
@@ -613,12 +618,26 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         ax = __fmaf_rn(k, dx, ax);
         ay = __fmaf_rn(k, dy, ay);
     };
+    auto append = [&](int e, float cx, float cy, float m) {   // record e of the list
+        lxy[(e >> 1) * 4 + (e & 1)] = cx;
+        lxy[(e >> 1) * 4 + 2 + (e & 1)] = cy;
+        lm[e] = m;
+    };
     auto flush = [&]() {
+        if ((lcount & 1) && lane == 0) append(lcount, FAR_AWAY, FAR_AWAY, 0.f);   // odd count: a massless partner
         __syncwarp();
-#pragma unroll 4
-        for (int k = 0; k < lcount; k++) {
-            const float4 c = lst[k];
-            add(c.x, c.y, c.z);
+        const int pairs = (lcount + 1) >> 1;
+#pragma unroll 2
+        for (int k = 0; k < pairs; k++) {
+            const ulonglong2 c = reinterpret_cast<const ulonglong2*>(lxy)[k];     // (cx0, cx1) (cy0, cy1)
+            const uint64_t m2 = reinterpret_cast<const uint64_t*>(lm)[k];          // (m0, m1)
+            const uint64_t dx = sub2(c.x, X2), dy = sub2(c.y, Y2);
+            const uint64_t r2 = fma2(dy, dy, fma2(dx, dx, E2));
+            float r0, r1;
+            up2(r2, r0, r1);
+            const uint64_t k2 = mul2(pk2(rcp_approx(r0), rcp_approx(r1)), m2);
+            AX2 = fma2(k2, dx, AX2);
+            AY2 = fma2(k2, dy, AY2);
         }
         __syncwarp();
         lcount = 0;
@@ -670,7 +689,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         const unsigned rejm = __ballot_sync(FULLM, rej);
         const unsigned below = (1u << lane) - 1u;
         if (COUNT) { c_exam += __popc(__ballot_sync(FULLM, present)); c_inter += __popc(accm); }
-        if (accp) lst[lcount + __popc(accm & below)] = rec;
+        if (accp) append(lcount + __popc(accm & below), rec.x, rec.y, rec.z);
         lcount += __popc(accm);
         const int nrej = __popc(rejm);
         if (qtop + nrej > WL_QCAP) { overflow = true; break; }
@@ -710,6 +729,13 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         }
     }
     flush();
+    {
+        float a0, a1, b0, b1;
+        up2(AX2, a0, a1);
+        up2(AY2, b0, b1);
+        ax += a0 + a1;
+        ay += b0 + b1;
+    }
     if (valid) acc[body] = make_float4(ax, ay, 0.f, 0.f);
     if (overflow && lane == 0) atomicOr(&counters[4], 1ull);
     if (COUNT && lane == 0) {
