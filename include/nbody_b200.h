@@ -226,6 +226,13 @@ int nb_stats(nb_context* ctx, const float* pos, const float* vel, int n, int tar
 int nb_ic_uniform_ellipsoid(nb_context* ctx, float* pos, float* vel, int offset, int count, uint64_t seed, double cx, double cy,
                             double rx, double ry, double z_half_height, float mass, float central_mass, float vx, float vy,
                             void* stream);
+/* UniformBox (src/InitialConditions.cu:78-107) with the same counter-based generator: bodies [offset, offset+count)
+ * uniform in the box of size (sx, sy) centred on (cx, cy) -- in R3 (dim = 3) z is drawn from the y range, as the
+ * reference does (:85) -- mass ~ U[mass_lo, mass_hi); `vel` (slice-local, may be NULL) gets a speed ~ U[speed_lo,
+ * speed_hi) in a random in-plane direction plus the bulk velocity (vx, vy). */
+int nb_ic_uniform_box(nb_context* ctx, float* pos, float* vel, int offset, int count, uint64_t seed, double cx, double cy, double sx,
+                      double sy, int dim, double mass_lo, double mass_hi, double speed_lo, double speed_hi, float vx, float vy,
+                      void* stream);
 /* The velocity loop of DiskModel::initialize (src/InitialConditions.cu:169-192) after one force evaluation:
  * v = sqrt(|a| r), tangential, in the reference's FP32 arithmetic; acc and vel are slice-local float4[count]. */
 int nb_ic_disk_velocities(nb_context* ctx, const float* pos, const float* acc, float* vel, int begin, int count, float cx, float cy,

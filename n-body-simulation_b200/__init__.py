@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "nb_direct_last_launch",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
-    "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_disk_velocities",
+    "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities",
     "nb_bh3d_accel", "nb_bh3d_accel_groups", "nb_bh3d_stages_host", "nb_bh3d_export_tree", "nb_bh3d_last_counters",
 ]
 
@@ -73,6 +73,7 @@ def lib():
         L.nb_verlet_dkd_kick_drift.argtypes = [vp, vp, vp, vp, i, i, f, vp]
         d = C.c_double
         L.nb_ic_uniform_ellipsoid.argtypes = [vp, vp, vp, i, i, C.c_uint64, d, d, d, d, d, f, f, f, f, vp]
+        L.nb_ic_uniform_box.argtypes = [vp, vp, vp, i, i, C.c_uint64, d, d, d, d, i, d, d, d, d, f, f, vp]
         L.nb_ic_disk_velocities.argtypes = [vp, vp, vp, vp, i, i, f, f, i, f, f, vp]
         L.nb_stats.argtypes = [vp, vp, vp, i, i, i, i, C.POINTER(C.c_double), vp]
         L.nb_integrate_substep.argtypes = [vp, vp, vp, vp, vp, i, i, f, i, C.c_double, i, C.c_double, vp]
@@ -231,6 +232,14 @@ class Engine:
                                                   offset, count, seed, centre[0], centre[1], radius[0], radius[1],
                                                   z_half_height, mass, central_mass, bulk_velocity[0], bulk_velocity[1],
                                                   _stream_ptr(stream)), "nb_ic_uniform_ellipsoid")
+
+    def ic_uniform_box(self, pos, offset, count, seed=1, centre=(0.0, 0.0), size=(60000.0, 60000.0), dim=2,
+                       mass_range=(70000.0, 70000.0), speed_range=(0.0, 0.0), bulk_velocity=(0.0, 0.0), vel=None, stream=None):
+        """UniformBox (src/InitialConditions.cu:78-107) written straight into device memory."""
+        self._check(lib().nb_ic_uniform_box(self._h, pos.data_ptr(), vel.data_ptr() if vel is not None else None, offset, count,
+                                            seed, centre[0], centre[1], size[0], size[1], dim, mass_range[0], mass_range[1],
+                                            speed_range[0], speed_range[1], bulk_velocity[0], bulk_velocity[1],
+                                            _stream_ptr(stream)), "nb_ic_uniform_box")
 
     def ic_disk_velocities(self, pos, acc, vel, begin, count, centre=(0.0, 0.0), dim=2, bulk_velocity=(0.0, 0.0), stream=None):
         self._check(lib().nb_ic_disk_velocities(self._h, pos.data_ptr(), acc.data_ptr(), vel.data_ptr(), begin, count,

@@ -352,6 +352,7 @@ __global__ void __launch_bounds__(256) emit3_kernel(TreeView3 t, const float4* _
 constexpr int W3_WARPS = 4;
 constexpr int W3_QCAP = 1024;
 constexpr int W3_LCAP = 64;
+constexpr float FAR_AWAY3 = 3.0e18f;           // coordinate of a padding record: zero mass, contributes exactly 0
 
 __device__ __forceinline__ float rsqrt3_approx(float x) {
     float r;
@@ -369,7 +370,9 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
                                                                 int group_begin, int group_count, float4* __restrict__ acc,
                                                                 unsigned long long* __restrict__ counters) {
     __shared__ uint32_t q_s[W3_WARPS][W3_QCAP];
-    __shared__ float4 l_s[W3_WARPS][W3_LCAP];
+    // pending accepted records, two per slot (FP32x2 evaluation): (cx0, cx1, cy0, cy1) and (cz0, cz1, m0, m1)
+    __shared__ float4 lxy_s[W3_WARPS][W3_LCAP / 2];
+    __shared__ float4 lzm_s[W3_WARPS][W3_LCAP / 2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned FULLM = 0xffffffffu;
     const int g = blockIdx.x * W3_WARPS + warp;
@@ -388,8 +391,11 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         bz0 = fminf(bz0, __shfl_xor_sync(FULLM, bz0, o)); bz1 = fmaxf(bz1, __shfl_xor_sync(FULLM, bz1, o));
     }
     float ax = 0.f, ay = 0.f, az = 0.f;
+    uint64_t AX2 = 0ull, AY2 = 0ull, AZ2 = 0ull;   // packed partial sums of the list evaluation (even / odd records)
+    const uint64_t X2 = pk2(x, x), Y2 = pk2(y, y), Z2 = pk2(z, z), E2 = pk2(eps, eps);
     uint32_t* const q = q_s[warp];
-    float4* const lst = l_s[warp];
+    float* const lxy = reinterpret_cast<float*>(lxy_s[warp]);
+    float* const lzm = reinterpret_cast<float*>(lzm_s[warp]);
     int qtop = 0, lcount = 0;
     unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
     int c_depth = 0;
@@ -404,12 +410,30 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         ay = __fmaf_rn(k, dy, ay);
         az = __fmaf_rn(k, dz, az);
     };
+    auto append = [&](int e, const float4& c) {   // record e of the list
+        const int at = (e >> 1) * 4 + (e & 1);
+        lxy[at] = c.x;
+        lxy[at + 2] = c.y;
+        lzm[at] = c.z;
+        lzm[at + 2] = c.w;
+    };
     auto flush = [&]() {
+        if ((lcount & 1) && lane == 0) append(lcount, make_float4(FAR_AWAY3, FAR_AWAY3, FAR_AWAY3, 0.f));   // massless partner
         __syncwarp();
-#pragma unroll 4
-        for (int k = 0; k < lcount; k++) {
-            const float4 c = lst[k];
-            add(c.x, c.y, c.z, c.w);
+        const int pairs = (lcount + 1) >> 1;
+#pragma unroll 2
+        for (int k = 0; k < pairs; k++) {
+            const ulonglong2 a = reinterpret_cast<const ulonglong2*>(lxy)[k];   // (cx0, cx1) (cy0, cy1)
+            const ulonglong2 b = reinterpret_cast<const ulonglong2*>(lzm)[k];   // (cz0, cz1) (m0, m1)
+            const uint64_t dx = sub2(a.x, X2), dy = sub2(a.y, Y2), dz = sub2(b.x, Z2);
+            const uint64_t r2 = fma2(dz, dz, fma2(dy, dy, fma2(dx, dx, E2)));
+            float r0, r1;
+            up2(r2, r0, r1);
+            const uint64_t inv = pk2(rsqrt3_approx(r0), rsqrt3_approx(r1));
+            const uint64_t k2 = mul2(mul2(mul2(inv, inv), inv), b.y);
+            AX2 = fma2(k2, dx, AX2);
+            AY2 = fma2(k2, dy, AY2);
+            AZ2 = fma2(k2, dz, AZ2);
         }
         __syncwarp();
         lcount = 0;
@@ -462,7 +486,7 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         const unsigned rejm = __ballot_sync(FULLM, rej);
         const unsigned below = (1u << lane) - 1u;
         if (COUNT) { c_exam += __popc(__ballot_sync(FULLM, present)); c_inter += __popc(accm); }
-        if (accp) lst[lcount + __popc(accm & below)] = rec;
+        if (accp) append(lcount + __popc(accm & below), rec);
         lcount += __popc(accm);
         const int nrej = __popc(rejm);
         if (qtop + nrej > W3_QCAP) { overflow = true; break; }
@@ -503,6 +527,12 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         }
     }
     flush();
+    {
+        float a0, a1;
+        up2(AX2, a0, a1); ax += a0 + a1;
+        up2(AY2, a0, a1); ay += a0 + a1;
+        up2(AZ2, a0, a1); az += a0 + a1;
+    }
     if (valid) acc[body] = make_float4(ax, ay, az, 0.f);
     if (overflow && lane == 0) atomicOr(&counters[4], 1ull);
     if (COUNT && lane == 0) {

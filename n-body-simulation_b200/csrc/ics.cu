@@ -3,6 +3,8 @@
 // device), same shapes as the reference's generators:
 //   UniformEllipsoid (src/InitialConditions.cu:111-144): phi ~ U[0, 2 pi), lambda ~ U[0.02, 1),
 //       pos = centre + radius * lambda * (cos phi, sin phi), z = 0 (or U[-h, h] for the R3 variant), mass, bulk velocity
+//   UniformBox (:78-107): x, y (and z in R3, which the reference draws from the y range, :85) uniform in the box,
+//       mass ~ U[massRange], speed ~ U[velRange] in a random in-plane direction plus the bulk velocity
 //   DiskModel (:153-196): body `offset` becomes the central mass; after ONE force evaluation every body gets the
 //       tangential speed v = sqrt(|a| r) -- nb_ic_disk_velocities, the loop of :169-192 with its FP32 arithmetic.
 #include "common.cuh"
@@ -36,6 +38,26 @@ __global__ void ellipsoid_kernel(float4* __restrict__ pos, float4* __restrict__ 
     if (i == 0 && central_mass >= 0.f) p = make_float4((float)cx, (float)cy, 0.f, central_mass);   // :157
     pos[offset + i] = p;
     if (vel) vel[i] = make_float4(vx, vy, 0.f, 0.f);
+}
+
+__global__ void box_kernel(float4* __restrict__ pos, float4* __restrict__ vel, int offset, int count, unsigned long long seed,
+                           double cx, double cy, double sx, double sy, int dim, double m0, double m1, double v0, double v1,
+                           float bvx, float bvy) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    // explicit _rn operations: no FMA contraction, so the doubles are the host generator's bit for bit
+    auto lerp = [](double a, double w, double u) { return __dadd_rn(a, __dmul_rn(w, u)); };
+    float4 p;
+    p.x = (float)lerp(cx, sx, uniform01(seed, 0, i) - 0.5);
+    p.y = (float)lerp(cy, sy, uniform01(seed, 1, i) - 0.5);
+    p.z = dim == 3 ? (float)lerp(cy, sy, uniform01(seed, 2, i) - 0.5) : 0.f;   // :85 uses the y range for z
+    p.w = (float)lerp(m0, m1 - m0, uniform01(seed, 3, i));
+    pos[offset + i] = p;
+    if (vel) {
+        const double phi = uniform01(seed, 4, i) * 6.283185307179586;
+        const double v = lerp(v0, v1 - v0, uniform01(seed, 5, i));
+        vel[i] = make_float4((float)(v * cos(phi)) + bvx, (float)(v * sin(phi)) + bvy, 0.f, 0.f);   // :101
+    }
 }
 
 __global__ void disk_velocity_kernel(const float4* __restrict__ pos, const float4* __restrict__ acc, float4* __restrict__ vel,
@@ -73,6 +95,19 @@ int nb_ic_uniform_ellipsoid(nb_context* ctx, float* pos, float* vel, int offset,
     if (count == 0) return NB_OK;
     ellipsoid_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, offset, count, seed, cx, cy, rx,
                                                                            ry, z_half_height, mass, central_mass, vx, vy);
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
+
+int nb_ic_uniform_box(nb_context* ctx, float* pos, float* vel, int offset, int count, uint64_t seed, double cx, double cy, double sx,
+                      double sy, int dim, double mass_lo, double mass_hi, double speed_lo, double speed_hi, float vx, float vy,
+                      void* stream) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
+    if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
+    if (count == 0) return NB_OK;
+    box_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, offset, count, seed, cx, cy, sx, sy,
+                                                                     dim, mass_lo, mass_hi, speed_lo, speed_hi, vx, vy);
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
 }

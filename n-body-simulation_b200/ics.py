@@ -45,6 +45,24 @@ def uniform_disk(n, seed=1, radius=30000.0, mass=70000.0, central_mass=10000.0, 
     return pos
 
 
+def uniform_box(n, seed=1, centre=(0.0, 0.0), size=(60000.0, 60000.0), space_r3=False, mass_range=(70000.0, 70000.0),
+                speed_range=(0.0, 0.0), bulk_velocity=(0.0, 0.0)):
+    """UniformBox (src/InitialConditions.cu:78-107): (pos float32 [n,4], vel float32 [n,4]).  In R3 the z coordinate is
+    drawn from the y range, as the reference does (:85)."""
+    pos = np.zeros((n, 4), np.float32)
+    vel = np.zeros((n, 4), np.float32)
+    pos[:, 0] = (centre[0] + size[0] * (uniform01(seed, 0, n) - 0.5)).astype(np.float32)
+    pos[:, 1] = (centre[1] + size[1] * (uniform01(seed, 1, n) - 0.5)).astype(np.float32)
+    if space_r3:
+        pos[:, 2] = (centre[1] + size[1] * (uniform01(seed, 2, n) - 0.5)).astype(np.float32)
+    pos[:, 3] = (mass_range[0] + (mass_range[1] - mass_range[0]) * uniform01(seed, 3, n)).astype(np.float32)
+    phi = uniform01(seed, 4, n) * 6.283185307179586
+    v = speed_range[0] + (speed_range[1] - speed_range[0]) * uniform01(seed, 5, n)
+    vel[:, 0] = (v * np.cos(phi)).astype(np.float32) + np.float32(bulk_velocity[0])
+    vel[:, 1] = (v * np.sin(phi)).astype(np.float32) + np.float32(bulk_velocity[1])
+    return pos, vel
+
+
 def disk_velocities(pos, acc, centre=(0.0, 0.0), space_r3=False):
     """Tangential speeds v = sqrt(|a| r) from one force evaluation, src/InitialConditions.cu:169-192."""
     x = pos[:, 0] - np.float32(centre[0])

@@ -180,3 +180,29 @@ def test_device_initial_conditions_match_the_host_generators(engine, pkg):
     torch.cuda.synchronize()
     want = pkg.ics.disk_velocities(host, acc.cpu().numpy())
     assert np.array_equal(vel.cpu().numpy(), want)
+
+
+def test_device_uniform_box_matches_the_host_generator(engine, pkg):
+    """nb_ic_uniform_box against ics.uniform_box: positions and masses bit for bit (explicitly rounded double
+    arithmetic on both sides), velocities within one FP32 ulp (double cos/sin of the device vs the host)."""
+    import torch
+    n = 100000
+    for r3 in (False, True):
+        kw = dict(seed=11, centre=(500.0, -2500.0), size=(40000.0, 10000.0), mass_range=(10.0, 90000.0),
+                  speed_range=(5.0, 250.0), bulk_velocity=(30.0, -4.0))
+        hp, hv = pkg.ics.uniform_box(n, space_r3=r3, **kw)
+        pos = torch.zeros(n + 7, 4, device="cuda")
+        vel = torch.zeros(n, 4, device="cuda")
+        engine.ic_uniform_box(pos, 7, n, dim=3 if r3 else 2, vel=vel, **kw)
+        torch.cuda.synchronize()
+        dp, dv = pos.cpu().numpy(), vel.cpu().numpy()
+        assert np.all(dp[:7] == 0) and np.array_equal(dp[7:], hp)
+        assert np.all(np.abs(hp[:, 0] - 500.0) <= 20000.0) and np.all(np.abs(hp[:, 1] + 2500.0) <= 5000.0)
+        assert (hp[:, 2].std() > 1000.0) == r3
+        ulp = np.spacing(np.maximum(np.abs(hv[:, :2]), 1.0).astype(np.float32))
+        assert np.all(np.abs(dv[:, :2] - hv[:, :2]) <= ulp) and np.mean(dv[:, :2] == hv[:, :2]) > 0.999
+        assert np.all(dv[:, 2:] == 0)
+    # empty range and bad arguments
+    engine.ic_uniform_box(pos, 0, 0)
+    with pytest.raises(RuntimeError):
+        engine.ic_uniform_box(pos, 0, 10, dim=4)
