@@ -87,6 +87,10 @@ struct nb_bh_state {
     GraphKey graph_key{};
     cudaGraphExec_t graph_exec = nullptr;
     cudaStream_t capture_stream = nullptr;
+    // the SFC sort (target order) and the tree-key sort + tree build do not depend on each other: the former runs on
+    // a side stream between a fork and a join event (each radix pass fills only a fraction of the machine)
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
 };
 
 namespace {
@@ -581,6 +585,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
     // pending accepted records, two per slot so that the evaluation runs on FP32x2: (cx0, cx1, cy0, cy1) and (m0, m1)
     __shared__ float4 lxy_s[WL_WARPS][WL_LCAP / 2];
     __shared__ float2 lm_s[WL_WARPS][WL_LCAP / 2];
+    __shared__ float4 amb_s[WL_WARPS][32];   // undecided records of the current batch
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned FULLM = 0xffffffffu;
     const int g = blockIdx.x * WL_WARPS + warp;
@@ -606,6 +611,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
     uint32_t* const q = q_s[warp];
     float* const lxy = reinterpret_cast<float*>(lxy_s[warp]);
     float* const lm = reinterpret_cast<float*>(lm_s[warp]);
+    float4* const ambuf = amb_s[warp];
     int qtop = 0, lcount = 0;
     unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
     int c_depth = 0;
@@ -667,27 +673,35 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
             }
         }
         // ---- undecided records: the real unanimous vote --------------------------------------------------
-        unsigned ambm = __ballot_sync(FULLM, amb);
-        while (ambm) {
-            const int src = __ffs(ambm) - 1;
-            ambm &= ambm - 1;
-            const float cx = __shfl_sync(FULLM, rec.x, src), cy = __shfl_sync(FULLM, rec.y, src);
-            const float cm = __shfl_sync(FULLM, rec.z, src), ct = __shfl_sync(FULLM, rec.w, src);
-            const float dx = cx - x, dy = cy - y;
-            const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
-            if (__all_sync(FULLM, ct <= r)) {
-                const float k = rcp_approx(r) * cm;
-                ax = __fmaf_rn(k, dx, ax);
-                ay = __fmaf_rn(k, dy, ay);
-                if (COUNT) c_inter++;
-            } else if (lane == src) {
-                rej = true;
+        // They are compacted into shared memory and read back as broadcasts (one LDS.128 per record instead of
+        // four shuffles and a find-first-set); rejections come back as a bit per compacted slot.
+        const unsigned ambm = __ballot_sync(FULLM, amb);
+        const unsigned below = (1u << lane) - 1u;
+        if (ambm) {
+            const int slot = __popc(ambm & below);
+            if (amb) ambuf[slot] = rec;
+            __syncwarp();
+            const int na = __popc(ambm);
+            unsigned rejk = 0u, bit = 1u;
+#pragma unroll 2
+            for (int k = 0; k < na; k++, bit += bit) {
+                const float4 c = ambuf[k];
+                const float dx = c.x - x, dy = c.y - y;
+                const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+                if (__all_sync(FULLM, c.w <= r)) {
+                    const float kk = rcp_approx(r) * c.z;
+                    ax = __fmaf_rn(kk, dx, ax);
+                    ay = __fmaf_rn(kk, dy, ay);
+                    if (COUNT) c_inter++;
+                } else {
+                    rejk |= bit;
+                }
             }
+            if (amb && ((rejk >> slot) & 1u)) rej = true;
         }
         // ---- accepted -> interaction list, rejected -> node LIFO -----------------------------------------
         const unsigned accm = __ballot_sync(FULLM, accp);
         const unsigned rejm = __ballot_sync(FULLM, rej);
-        const unsigned below = (1u << lane) - 1u;
         if (COUNT) { c_exam += __popc(__ballot_sync(FULLM, present)); c_inter += __popc(accm); }
         if (accp) append(lcount + __popc(accm & below), rec.x, rec.y, rec.z);
         lcount += __popc(accm);
@@ -761,8 +775,13 @@ void free_state(nb_bh_state* st) {
     if (!st) return;
     if (st->graph_exec) cudaGraphExecDestroy(st->graph_exec);
     if (st->capture_stream) cudaStreamDestroy(st->capture_stream);
+    if (st->side_stream) cudaStreamDestroy(st->side_stream);
+    if (st->fork_ev) cudaEventDestroy(st->fork_ev);
+    if (st->join_ev) cudaEventDestroy(st->join_ev);
     st->graph_exec = nullptr;
     st->capture_stream = nullptr;
+    st->side_stream = nullptr;
+    st->fork_ev = st->join_ev = nullptr;
     void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
                     st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->ghist, st->clink, st->spos, st->psum, st->psum_blk,
                     st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
@@ -823,6 +842,9 @@ int ensure_state(nb_context* ctx, int n) {
     rc |= alloc(ctx, &st->root_rec, 2);
     rc |= alloc(ctx, &st->counters, 8);
     if (rc) return NB_ERR_CUDA;
+    NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->side_stream, cudaStreamNonBlocking));
+    NB_CUDA(ctx, cudaEventCreateWithFlags(&st->fork_ev, cudaEventDisableTiming));
+    NB_CUDA(ctx, cudaEventCreateWithFlags(&st->join_ev, cudaEventDisableTiming));
     NB_CUDA(ctx, cudaMemset(st->ticket, 0, sizeof(unsigned int)));
     NB_CUDA(ctx, cudaMemset(st->counters, 0, 8 * sizeof(unsigned long long)));
     if (keep_bounds) {
@@ -853,28 +875,51 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
         keys_kernel<<<(n + KEYS_PER_BLOCK - 1) / KEYS_PER_BLOCK, KEYS_THREADS, 0, stream>>>(pos, n, st->bounds, st->key32[0],
                                                                                           st->key64[0], st->ghist);
     }
+    static const bool no_fork = getenv("NB_BH_NO_FORK") != nullptr;   // measurement switch: everything on one stream
+    const bool fork = upto >= 3 && !no_fork;
     if (upto >= 3) {
+        cudaStream_t sfc_stream = stream;
+        if (fork) {
+            NB_CUDA(ctx, cudaEventRecord(st->fork_ev, stream));
+            NB_CUDA(ctx, cudaStreamWaitEvent(st->side_stream, st->fork_ev, 0));
+            sfc_stream = st->side_stream;
+        }
         rc = radix_sort<uint32_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key32, st->idx32, n, 32, 0,
-                                  &st->sfc_sel, stream);
-        if (rc) return rc;
+                                  &st->sfc_sel, sfc_stream);
+        if (fork) {   // recorded even after a failed launch, so that a capture in progress can still be joined
+            cudaEventRecord(st->join_ev, st->side_stream);
+        }
+        if (rc) { if (fork) cudaStreamWaitEvent(stream, st->join_ev, 0); return rc; }
         rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n, 64, 4,
                                   &st->tree_sel, stream);
-        if (rc) return rc;
+        if (rc) { if (fork) cudaStreamWaitEvent(stream, st->join_ev, 0); return rc; }
     }
     if (upto >= 4 && n >= 2) {
         const int chunks = (n + SCAN_CHUNK - 1) / SCAN_CHUNK;
         const uint64_t* K = st->key64[st->tree_sel];
-        gather_scan_kernel<<<chunks, SCAN_THREADS, 0, stream>>>(pos, st->idx64[st->tree_sel], n, st->spos, st->psum,
-                                                               st->psum_blk);
-        scan_totals_kernel<D3><<<1, 1024, 0, stream>>>(st->psum_blk, chunks);
+        // the mass prefix sums (side stream, behind the SFC sort) and the node boundaries both follow from the sorted
+        // tree keys alone; the emit kernel needs both
+        cudaStream_t sums_stream = stream;
+        if (fork) {
+            NB_CUDA(ctx, cudaEventRecord(st->fork_ev, stream));
+            NB_CUDA(ctx, cudaStreamWaitEvent(st->side_stream, st->fork_ev, 0));
+            sums_stream = st->side_stream;
+        }
+        gather_scan_kernel<<<chunks, SCAN_THREADS, 0, sums_stream>>>(pos, st->idx64[st->tree_sel], n, st->spos, st->psum,
+                                                                    st->psum_blk);
+        scan_totals_kernel<D3><<<1, 1024, 0, sums_stream>>>(st->psum_blk, chunks);
+        if (fork) cudaEventRecord(st->join_ev, st->side_stream);
         const int bchunks = (n - 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
         boundary_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk);
         scan_totals_kernel<int><<<1, 1024, 0, stream>>>(st->flag_blk, bchunks);
+        if (fork) NB_CUDA(ctx, cudaStreamWaitEvent(stream, st->join_ev, 0));
         TreeView tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, st->ext_a, st->ext_c, st->ext_r, n};
         emit_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->bounds, theta, st->cblk,
                                                              reinterpret_cast<uint32_t*>(st->clink), st->node_first,
                                                              st->node_last, st->node_level, st->node_top, st->root,
                                                              st->root_rec);
+    } else if (fork) {
+        NB_CUDA(ctx, cudaStreamWaitEvent(stream, st->join_ev, 0));   // no tree stage: join behind the SFC sort
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
