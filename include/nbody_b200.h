@@ -15,6 +15,8 @@
  * The entry points here replace exactly those calls.  Conventions:
  *   - plain C: opaque handle, int status (0 = NB_OK), pointers and sizes only, no C++ or torch types;
  *   - body layout = the reference's float4 (x, y, z, mass), G = 1, softening added un-squared to r^2
+ *     (softening must be >= 0; 0 is raised to 1e-20 so that the self term, which the reference includes, stays
+ *     0 instead of the reference's 0 * inf = NaN -- no other term changes at FP32 resolution)
  *     (src/DirectComputeKernels.cu:26,64); `dim` 2 selects the reference's 2D law m*d/(eps+r^2), 3 the
  *     Newtonian m*d/(eps+r^2)^(3/2);
  *   - `pos`/`acc` device pointers are owned by the caller (NbodySystem::device, src/NbodySystem.h:17-26);

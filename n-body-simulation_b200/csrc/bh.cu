@@ -986,6 +986,8 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
                        int group_begin, int group_count, void* stream) {
     int rc = check_args(ctx, pos, acc, n, theta);
     if (rc) return rc;
+    if (!nb_softening_ok(softening)) return nb_fail(ctx, NB_ERR_INVALID, "softening must be >= 0");
+    softening = nb_effective_softening(softening);
     if (n == 0) return NB_OK;
     const int groups = (n + 31) / 32;
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)

@@ -668,6 +668,8 @@ int nb_bh3d_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, f
     if (n > (1 << 28)) return nb_fail(ctx, NB_ERR_INVALID, "n exceeds 2^28 bodies");
     if (n > 0 && (!pos || !acc)) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
     if (!(theta > 0.f)) return nb_fail(ctx, NB_ERR_INVALID, "theta must be > 0");
+    if (!nb_softening_ok(softening)) return nb_fail(ctx, NB_ERR_INVALID, "softening must be >= 0");
+    softening = nb_effective_softening(softening);
     if (n == 0) return NB_OK;
     const int groups = (n + 31) / 32;
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)

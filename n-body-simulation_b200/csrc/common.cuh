@@ -48,6 +48,13 @@ inline int nb_fail(nb_context* ctx, int code, const char* what, cudaError_t e = 
         if (e__ != cudaSuccess) return nb_fail((ctx), NB_ERR_CUDA, #call, e__); \
     } while (0)
 
+// Softening: the reference adds eps un-squared to r^2 and includes the self term, so eps = 0 turns every result into
+// 0 * inf = NaN (src/DirectComputeKernels.cu:23-30).  A floor of 1e-20 -- far below the FP32
+// resolution of any separation that is not itself zero -- keeps the self term at exactly 0 and changes nothing else.
+// Negative or NaN softening is an argument error.
+inline bool nb_softening_ok(float eps) { return eps >= 0.f; }
+inline float nb_effective_softening(float eps) { return eps > 1e-20f ? eps : 1e-20f; }
+
 // Grows a scratch buffer (stream-ordered callers must not have work in flight on the old buffer; the
 // engine only grows between evaluations, after a device synchronise).
 inline int nb_reserve(nb_context* ctx, void** ptr, size_t* have, size_t want) {

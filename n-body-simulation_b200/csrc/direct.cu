@@ -228,6 +228,8 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
                      int dim, float softening, int flags, cudaStream_t stream) {
     if (!ctx) return NB_ERR_INVALID;
     if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
+    if (!nb_softening_ok(softening)) return nb_fail(ctx, NB_ERR_INVALID, "softening must be >= 0");
+    softening = nb_effective_softening(softening);
     if (n < 0 || target_begin < 0 || target_count < 0 || (long long)target_begin + target_count > n)
         return nb_fail(ctx, NB_ERR_INVALID, "target slice outside [0, n)");
     if (target_count == 0) return NB_OK;
@@ -357,6 +359,8 @@ int noalloc_fail(int code, const char* what, cudaError_t e = cudaSuccess) { retu
 extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int dim, float softening, void* stream) {
     if (dim != 2 && dim != 3) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: dim must be 2 or 3");
     if (n < 0) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: n must be >= 0");
+    if (!nb_softening_ok(softening)) return noalloc_fail(NB_ERR_INVALID, "nb_direct_accel_noalloc: softening must be >= 0");
+    softening = nb_effective_softening(softening);
     if (n > NB_NOALLOC_MAX_BODIES)
         return noalloc_fail(NB_ERR_TOO_LARGE,
                             "nb_direct_accel_noalloc: n exceeds NB_NOALLOC_MAX_BODIES (262144), the static scratch "

@@ -157,3 +157,39 @@ def test_bad_arguments_are_rejected(engine, pkg):
         engine.direct_accel(pos, acc, 4, EPS)
     with pytest.raises(pkg.NbodyError):
         engine.direct_accel_slice(pos, 10, 10, acc, 3, EPS)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_zero_softening_keeps_the_self_term_at_zero(engine, pkg, dim):
+    """The reference includes the self term, so softening = 0 makes every result NaN there
+    (src/DirectComputeKernels.cu:23-30); here it is floored at 1e-20 and the sum equals the FP64 sum over j != i.
+    Negative or NaN softening is rejected."""
+    import torch
+    n = 700
+    pos = pkg.ics.uniform_disk(n, seed=77, z_half_height=2000.0 if dim == 3 else 0.0)
+    d = pos[None, :, :3].astype(np.float64) - pos[:, None, :3].astype(np.float64)
+    if dim == 2:
+        d[:, :, 2] = 0.0
+    r2 = (d * d).sum(-1)
+    np.fill_diagonal(r2, 1.0)
+    w = pos[None, :, 3].astype(np.float64) / (r2 ** 1.5 if dim == 3 else r2)
+    np.fill_diagonal(w, 0.0)
+    want = (w[:, :, None] * d).sum(1)
+    acc = torch.full((n, 4), 7.0, device="cuda")
+    engine.direct_accel(torch.from_numpy(pos).cuda(), acc, dim, 0.0)
+    torch.cuda.synchronize()
+    got = acc.cpu().numpy()
+    assert np.isfinite(got).all()
+    err = np.linalg.norm(got[:, :3] - want, axis=1) / np.linalg.norm(want, axis=1)
+    assert err.max() < 1e-5, err.max()
+    if dim == 2:
+        bh = torch.zeros(n, 4, device="cuda")
+        engine.bh_accel(torch.from_numpy(pos).cuda(), bh, 1e-3, 0.0)      # tiny theta: the walk degenerates to the direct sum
+        torch.cuda.synchronize()
+        e2 = np.linalg.norm(bh.cpu().numpy()[:, :2] - want[:, :2], axis=1) / np.linalg.norm(want[:, :2], axis=1)
+        assert np.isfinite(bh.cpu().numpy()).all() and e2.max() < 1e-4, e2.max()
+    for bad in (-1.0, float("nan")):
+        with pytest.raises(RuntimeError):
+            engine.direct_accel(torch.from_numpy(pos).cuda(), acc, dim, bad)
+        with pytest.raises(RuntimeError):
+            engine.bh_accel(torch.from_numpy(pos).cuda(), acc, 0.5, bad)
