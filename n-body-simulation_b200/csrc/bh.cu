@@ -586,6 +586,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
     __shared__ float4 lxy_s[WL_WARPS][WL_LCAP / 2];
     __shared__ float2 lm_s[WL_WARPS][WL_LCAP / 2];
     __shared__ float4 amb_s[WL_WARPS][32];   // undecided records of the current batch
+    __shared__ float2 wit_s[WL_WARPS][4];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned FULLM = 0xffffffffu;
     const int g = blockIdx.x * WL_WARPS + warp;
@@ -604,6 +605,17 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         bx1 = fmaxf(bx1, __shfl_xor_sync(FULLM, bx1, o));
         by0 = fminf(by0, __shfl_xor_sync(FULLM, by0, o));
         by1 = fmaxf(by1, __shfl_xor_sync(FULLM, by1, o));
+    }
+    // the targets that touch the four sides of the box: witnesses for early rejection
+    float2* const wit = wit_s[warp];
+    {
+        const unsigned m0 = __ballot_sync(FULLM, x == bx0), m1 = __ballot_sync(FULLM, x == bx1);
+        const unsigned m2 = __ballot_sync(FULLM, y == by0), m3 = __ballot_sync(FULLM, y == by1);
+        if (lane == __ffs(m0) - 1) wit[0] = make_float2(x, y);
+        if (lane == __ffs(m1) - 1) wit[1] = make_float2(x, y);
+        if (lane == __ffs(m2) - 1) wit[2] = make_float2(x, y);
+        if (lane == __ffs(m3) - 1) wit[3] = make_float2(x, y);
+        __syncwarp();
     }
     float ax = 0.f, ay = 0.f;
     uint64_t AX2 = 0ull, AY2 = 0ull;          // packed partial sums of the list evaluation (even / odd records)
@@ -669,7 +681,15 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
                 const float ddx = fmaxf(fmaxf(bx0 - rec.x, rec.x - bx1), 0.f);
                 const float ddy = fmaxf(fmaxf(by0 - rec.y, rec.y - by1), 0.f);
                 const float dmin = __fmaf_rn(ddy, ddy, __fmaf_rn(ddx, ddx, eps));
-                if (rec.w <= dmin * 0.999999f) accp = true; else amb = true;
+                if (rec.w <= dmin * 0.999999f) {
+                    accp = true;
+                } else {   // a second witness: the group's extreme target on the side the record lies on
+                    const float2 wa = wit[rec.x < bx0 ? 0 : 1], wb = wit[rec.y < by0 ? 2 : 3];
+                    const float dxa = rec.x - wa.x, dya = rec.y - wa.y, dxb = rec.x - wb.x, dyb = rec.y - wb.y;
+                    const float ra = __fmaf_rn(dya, dya, __fmaf_rn(dxa, dxa, eps));
+                    const float rb = __fmaf_rn(dyb, dyb, __fmaf_rn(dxb, dxb, eps));
+                    if (!(rec.w <= fminf(ra, rb))) rej = true; else amb = true;
+                }
             }
         }
         // ---- undecided records: the real unanimous vote --------------------------------------------------
