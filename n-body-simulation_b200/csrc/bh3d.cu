@@ -373,6 +373,7 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
     // pending accepted records, two per slot (FP32x2 evaluation): (cx0, cx1, cy0, cy1) and (cz0, cz1, m0, m1)
     __shared__ float4 lxy_s[W3_WARPS][W3_LCAP / 2];
     __shared__ float4 lzm_s[W3_WARPS][W3_LCAP / 2];
+    __shared__ float4 wit_s[W3_WARPS][6];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned FULLM = 0xffffffffu;
     const int g = blockIdx.x * W3_WARPS + warp;
@@ -389,6 +390,18 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         bx0 = fminf(bx0, __shfl_xor_sync(FULLM, bx0, o)); bx1 = fmaxf(bx1, __shfl_xor_sync(FULLM, bx1, o));
         by0 = fminf(by0, __shfl_xor_sync(FULLM, by0, o)); by1 = fmaxf(by1, __shfl_xor_sync(FULLM, by1, o));
         bz0 = fminf(bz0, __shfl_xor_sync(FULLM, bz0, o)); bz1 = fmaxf(bz1, __shfl_xor_sync(FULLM, bz1, o));
+    }
+    // the targets that touch the six faces of the box: witnesses for early rejection
+    float4* const wit = wit_s[warp];
+    {
+        const float ext[6] = {bx0, bx1, by0, by1, bz0, bz1};
+        const float mine[6] = {x, x, y, y, z, z};
+#pragma unroll
+        for (int f = 0; f < 6; f++) {
+            const unsigned m = __ballot_sync(FULLM, mine[f] == ext[f]);
+            if (lane == __ffs(m) - 1) wit[f] = make_float4(x, y, z, 0.f);
+        }
+        __syncwarp();
     }
     float ax = 0.f, ay = 0.f, az = 0.f;
     uint64_t AX2 = 0ull, AY2 = 0ull, AZ2 = 0ull;   // packed partial sums of the list evaluation (even / odd records)
@@ -460,7 +473,18 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
                 const float ddy = fmaxf(fmaxf(by0 - rec.y, rec.y - by1), 0.f);
                 const float ddz = fmaxf(fmaxf(bz0 - rec.z, rec.z - bz1), 0.f);
                 const float dmin = __fmaf_rn(ddz, ddz, __fmaf_rn(ddy, ddy, __fmaf_rn(ddx, ddx, eps)));
-                if (thr <= dmin * 0.999999f) accp = true; else amb = true;
+                if (thr <= dmin * 0.999999f) {
+                    accp = true;
+                } else {   // a second witness: the group's extreme target on the side the record lies on
+                    int sel;
+                    if (ddx >= ddy && ddx >= ddz) sel = rec.x < bx0 ? 0 : 1;
+                    else if (ddy >= ddz) sel = rec.y < by0 ? 2 : 3;
+                    else sel = rec.z < bz0 ? 4 : 5;
+                    const float4 wt = wit[sel];
+                    const float dxw = rec.x - wt.x, dyw = rec.y - wt.y, dzw = rec.z - wt.z;
+                    const float rw = __fmaf_rn(dzw, dzw, __fmaf_rn(dyw, dyw, __fmaf_rn(dxw, dxw, eps)));
+                    if (!(thr <= rw)) rej = true; else amb = true;
+                }
             }
         }
         unsigned ambm = __ballot_sync(FULLM, amb);
