@@ -108,8 +108,9 @@ def run_reference_arm(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "direct all-pairs N=1048576 uniform disk (R3), Leapfrog force evaluation", "n": N_BODIES,
-                       "softening": EPS},
+            "config": {"workload": f"direct all-pairs N={N_BODIES} uniform disk (R3), Leapfrog (Verlet_DKD) step",
+                       "n": N_BODIES, "softening": EPS, "dt": DT,
+                       "sampling": "each step evaluates a bounded slice of the targets against all sources (see cpu_baseline.sample)"},
             "cpu_baseline": {"value": val, "unit": "interactions/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
@@ -477,10 +478,10 @@ def main():
         line = {"metric": "interactions/s (direct, N=1M)", "value": value, "unit": "interactions/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"direct all-pairs N={n} uniform disk (R{dim}), Leapfrog (Verlet_DKD) step, "
-                                       f"target-sharded over {world} GPU(s), one NCCL all-gather of positions per step",
+                "config": {"workload": f"direct all-pairs N={n} uniform disk (R{dim}), Leapfrog (Verlet_DKD) step",
                            "n": n, "softening": EPS, "dt": DT, "l2": "flushed between timed iterations (256 MB write)",
-                           "parallelism": f"target-slice x{world}"},
+                           "parallelism": f"target-slice x{world}: targets sharded over {world} GPU(s), one NCCL "
+                                          f"all-gather of positions per step"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (launches_force + 2),
                 "roofline": roofline, "cpu_baseline": cpu_baseline}
         line.update(extra)
