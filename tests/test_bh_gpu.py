@@ -246,3 +246,40 @@ def test_sixteen_million_bodies_two_galaxies(pkg, oracle):
     assert np.median(e) < 5e-3 and e.max() < 0.1, (np.median(e), e.max())
     info = eng.device_info()
     eng.close()
+
+
+def test_call_sequence_keeps_no_stale_state(pkg):
+    """One engine through a random sequence of calls -- sizes on both sides of the graph-replay limit and of the
+    engine's current capacity (the scratch grows), repeated arguments (graph replay), changed theta / softening /
+    group ranges, the legacy default stream and a private one, stage queries in between -- must give, call for call,
+    what a fresh engine gives for the same arguments (the pipeline is deterministic, so bit for bit)."""
+    import torch
+    rng = np.random.default_rng(2024)
+    sizes = [33, 5000, 70000, 300000, 8192, 262144, 262145, 1000, 300000, 70000]
+    side = torch.cuda.Stream()
+    eng = pkg.Engine(0, 4096)
+    pools = {n: _dev(pkg.ics.clustered(n, seed=100 + k, sigma=200.0) if k % 2 else pkg.ics.uniform_disk(n, seed=100 + k))
+             for k, n in enumerate(sorted(set(sizes)))}
+    for it, n in enumerate(sizes * 2):
+        pos = pools[n]
+        theta = float(rng.choice([0.3, 0.5, 0.7]))
+        eps = float(rng.choice([1.01, 0.25]))
+        groups = (n + 31) // 32
+        g0 = int(rng.integers(0, groups)) if it % 3 == 1 else 0
+        gc = int(rng.integers(0, groups - g0 + 1)) if it % 3 == 1 else groups
+        stream = side if it % 4 == 2 else (0 if it % 4 == 3 else None)
+        acc = torch.full((n, 4), -3.0, device="cuda")
+        want = torch.full((n, 4), -3.0, device="cuda")
+        torch.cuda.synchronize()
+        for rep in range(3 if it % 2 else 1):     # repeats replay the captured graph where one exists
+            eng.bh_accel_groups(pos, acc, theta, eps, g0, gc, stream=stream)
+        torch.cuda.synchronize()
+        fresh = pkg.Engine(0, n)
+        fresh.bh_accel_groups(pos, want, theta, eps, g0, gc)
+        torch.cuda.synchronize()
+        fresh.close()
+        assert torch.equal(acc, want), (it, n, theta, eps, g0, gc)
+        if it % 5 == 0:
+            st = eng.bh_stages(pos)
+            assert np.all(np.diff(st["keys"][st["sorted_idx"]].astype(np.int64)) >= 0)
+    eng.close()

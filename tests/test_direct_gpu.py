@@ -193,3 +193,35 @@ def test_zero_softening_keeps_the_self_term_at_zero(engine, pkg, dim):
             engine.direct_accel(torch.from_numpy(pos).cuda(), acc, dim, bad)
         with pytest.raises(RuntimeError):
             engine.bh_accel(torch.from_numpy(pos).cuda(), acc, 0.5, bad)
+
+
+def test_call_sequence_keeps_no_stale_state(pkg):
+    """One engine through a sequence of direct-sum calls of changing size (the scratch grows), dimension, mass
+    pattern (uniform tiles hoist the mass, mixed ones do not), target slice and stream must give, call for call, the
+    bits a fresh engine gives."""
+    import torch
+    rng = np.random.default_rng(7)
+    side = torch.cuda.Stream()
+    eng = pkg.Engine(0, 1024)
+    for it, n in enumerate([513, 20000, 4096, 70001, 1, 20000, 131072, 3000]):
+        pos_h = pkg.ics.uniform_disk(n, seed=300 + it, z_half_height=2500.0)
+        if it % 2:
+            pos_h[:, 3] = rng.uniform(1.0, 9e4, n).astype(np.float32)
+        pos = torch.from_numpy(pos_h).cuda()
+        dim = 2 + it % 2
+        b = int(rng.integers(0, n)) if it % 3 == 2 else 0
+        cnt = int(rng.integers(0, n - b + 1)) if it % 3 == 2 else n
+        flags = pkg.NB_DIRECT_ORDERED if it % 4 == 3 else pkg.NB_DIRECT_AUTO
+        stream = side if it % 2 else None
+        got = torch.full((max(cnt, 1), 4), 5.0, device="cuda")
+        want = torch.full((max(cnt, 1), 4), 5.0, device="cuda")
+        torch.cuda.synchronize()
+        for _ in range(2):
+            eng.direct_accel_slice(pos, b, cnt, got, dim, 1.01, flags, stream=stream)
+        torch.cuda.synchronize()
+        fresh = pkg.Engine(0, n)
+        fresh.direct_accel_slice(pos, b, cnt, want, dim, 1.01, flags)
+        torch.cuda.synchronize()
+        fresh.close()
+        assert torch.equal(got, want), (it, n, dim, b, cnt, flags)
+    eng.close()
