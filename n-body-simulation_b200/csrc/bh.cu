@@ -55,6 +55,14 @@ struct nb_bh_state {
     uint32_t* os_status = nullptr;     // [12][os_stride] look-back status, os_stride = tiles * 256
     unsigned int* os_ticket = nullptr; // [12]
     size_t os_stride = 0, os_bytes = 0;
+    int32_t* fix_work = nullptr;       // positions of bodies in runs the five-pass tree-key sort leaves unsorted
+    // The five-pass sort reports (one store into mapped page-locked memory, no copy, no sync) when it had to fall
+    // back to the conditional full sort; the host then asks for eight plain passes for the next evaluations and
+    // probes again later.  A stale reading only costs time, never correctness.
+    uint32_t* h_full_flag = nullptr;   // host view
+    uint32_t* d_full_flag = nullptr;   // device alias of the same word
+    int full_sort_left = 0;
+    bool sort_full = false;
     float4* spos = nullptr;            // bodies in tree order: (x, y, m, -)
     D3* psum = nullptr;                // chunk-local inclusive prefix sums of (m, m x, m y)
     D3* psum_blk = nullptr;            // exclusive prefix of the chunk totals
@@ -78,10 +86,11 @@ struct nb_bh_state {
     // small systems are launch-bound (20 launches + 1 memset per evaluation): the whole evaluation is captured once
     // into a CUDA graph and replayed while the call's arguments stay the same
     struct GraphKey {
-        const float* pos; float* acc; int n, flags, group_begin, group_count, accumulate; float theta, eps;
+        const float* pos; float* acc; int n, flags, group_begin, group_count, accumulate; float theta, eps; bool sort_full;
         bool operator==(const GraphKey& o) const {
             return pos == o.pos && acc == o.acc && n == o.n && flags == o.flags && group_begin == o.group_begin &&
-                   group_count == o.group_count && accumulate == o.accumulate && theta == o.theta && eps == o.eps;
+                   group_count == o.group_count && accumulate == o.accumulate && theta == o.theta && eps == o.eps &&
+                   sort_full == o.sort_full;
         }
     };
     GraphKey graph_key{};
@@ -229,6 +238,93 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
 }
 
 #include "bh_shared.cuh"   // radix sort + chunked scans (shared with bh3d.cu), included inside this anonymous namespace
+
+// ------------------------------------------------------------------------------------------------------
+// Tree-key sort in five passes instead of eight.  The LSD passes over the upper 40 bits (20 tree levels) leave
+// the bodies ordered except inside runs that share those 40 bits -- bodies closer than 2^-20 of the box, a
+// handful in a million for anything but a collapsed system.  mark_runs_kernel collects the members of such runs,
+// fix_runs_kernel (one block) sorts them by the full key and puts them back into the same slots, stable by
+// current position, which is exactly what three more LSD passes would have produced.  More than FIX_CAP members:
+// a device flag switches on eight conditional passes (a full LSD sort from the current order -- ties keep their
+// order, so the result is again the stable sort) that otherwise return at once.
+// ------------------------------------------------------------------------------------------------------
+constexpr int HYBRID_LOW_BITS = 24;      // bits left to the fix-up
+constexpr int FIX_CAP = 2048;            // members of short-of-sorted runs one block can repair
+constexpr int N_SLOTS = N_DIGITS + 8;    // ticket / status areas: 12 regular passes + 8 conditional ones
+constexpr int FIX_COUNT_WORD = 32, FIX_FLAG_WORD = 33;   // in the 64-word ticket area (cleared with it)
+
+__global__ void __launch_bounds__(256) mark_runs_kernel(const uint64_t* __restrict__ K, int n, int32_t* __restrict__ work,
+                                                       uint32_t* __restrict__ count, uint32_t* __restrict__ full_sort) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool f = false;
+    if (i < n) {
+        const uint64_t hi = K[i] >> HYBRID_LOW_BITS;
+        f = (i > 0 && (K[i - 1] >> HYBRID_LOW_BITS) == hi) || (i + 1 < n && (K[i + 1] >> HYBRID_LOW_BITS) == hi);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, f);
+    if (m == 0u) return;
+    if (*reinterpret_cast<volatile uint32_t*>(full_sort)) return;   // already beyond repair: no more bookkeeping
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(count, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base + __popc(m) > FIX_CAP) {
+        if (lane == 0) *full_sort = 1u;
+        return;
+    }
+    if (f) work[base + __popc(m & ((1u << lane) - 1u))] = i;
+}
+
+template <typename T, typename Less>
+__device__ __forceinline__ void bitonic_sort_shared(T* a, int p2, Less less) {   // p2: power of two, whole block
+    for (int k = 2; k <= p2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < p2; t += blockDim.x) {
+                const int l = t ^ j;
+                if (l > t) {
+                    const bool up = (t & k) == 0;
+                    const T x = a[t], y = a[l];
+                    if (less(y, x) == up) { a[t] = y; a[l] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+struct FixRec { uint64_t key; int32_t pos; int32_t val; };
+
+__global__ void __launch_bounds__(1024) fix_runs_kernel(uint64_t* __restrict__ K, int32_t* __restrict__ V,
+                                                       const int32_t* __restrict__ work, const uint32_t* __restrict__ count,
+                                                       const uint32_t* __restrict__ full_sort, uint32_t* host_flag) {
+    __shared__ FixRec rec[FIX_CAP];
+    __shared__ int32_t slot[FIX_CAP];
+    const int m = (int)*count;
+    if (*full_sort) {   // too many for one block: the conditional passes that follow sort everything; tell the host
+        if (threadIdx.x == 0) *host_flag = 1u;
+        return;
+    }
+    if (m == 0) return;
+    int p2 = 2;
+    while (p2 < m) p2 <<= 1;
+    for (int j = threadIdx.x; j < p2; j += blockDim.x) {
+        if (j < m) {
+            const int p = work[j];
+            rec[j] = FixRec{K[p], p, V[p]};
+            slot[j] = p;
+        } else {
+            rec[j] = FixRec{~0ull, 0x7fffffff, 0};
+            slot[j] = 0x7fffffff;
+        }
+    }
+    __syncthreads();
+    bitonic_sort_shared(rec, p2, [](const FixRec& a, const FixRec& b) { return a.key < b.key || (a.key == b.key && a.pos < b.pos); });
+    bitonic_sort_shared(slot, p2, [](int32_t a, int32_t b) { return a < b; });
+    for (int j = threadIdx.x; j < m; j += blockDim.x) {
+        K[slot[j]] = rec[j].key;
+        V[slot[j]] = rec[j].val;
+    }
+}
 
 template <>
 __device__ __forceinline__ D3 shfl_up_t<D3>(D3 v, int o) {
@@ -795,6 +891,8 @@ void free_state(nb_bh_state* st) {
     if (!st) return;
     if (st->graph_exec) cudaGraphExecDestroy(st->graph_exec);
     if (st->capture_stream) cudaStreamDestroy(st->capture_stream);
+    if (st->h_full_flag) cudaFreeHost(st->h_full_flag);
+    st->h_full_flag = st->d_full_flag = nullptr;
     if (st->side_stream) cudaStreamDestroy(st->side_stream);
     if (st->fork_ev) cudaEventDestroy(st->fork_ev);
     if (st->join_ev) cudaEventDestroy(st->join_ev);
@@ -803,7 +901,7 @@ void free_state(nb_bh_state* st) {
     st->side_stream = nullptr;
     st->fork_ev = st->join_ev = nullptr;
     void* ptrs[] = {st->bounds, st->bounds_part, st->ticket, st->key32[0], st->key32[1], st->idx32[0], st->idx32[1],
-                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->ghist, st->clink, st->spos, st->psum, st->psum_blk,
+                    st->key64[0], st->key64[1], st->idx64[0], st->idx64[1], st->ghist, st->fix_work, st->clink, st->spos, st->psum, st->psum_blk,
                     st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk, st->cblk, st->node_first, st->node_last, st->node_level,
                     st->node_top, st->root, st->root_rec, st->counters};
     for (void* p : ptrs)
@@ -839,7 +937,8 @@ int ensure_state(nb_context* ctx, int n) {
         rc |= alloc(ctx, &st->key64[k], cap);
         rc |= alloc(ctx, &st->idx64[k], cap);
     }
-    const size_t os_words = (size_t)N_DIGITS * 256 + 64 + (size_t)N_DIGITS * 256 * sblocks;
+    const size_t os_words = (size_t)N_DIGITS * 256 + 64 + (size_t)N_SLOTS * 256 * sblocks;
+    rc |= alloc(ctx, &st->fix_work, (size_t)FIX_CAP);
     st->os_bytes = os_words * sizeof(uint32_t);
     rc |= alloc(ctx, &st->ghist, os_words);
     st->os_ticket = reinterpret_cast<unsigned int*>(st->ghist + N_DIGITS * 256);
@@ -862,6 +961,9 @@ int ensure_state(nb_context* ctx, int n) {
     rc |= alloc(ctx, &st->root_rec, 2);
     rc |= alloc(ctx, &st->counters, 8);
     if (rc) return NB_ERR_CUDA;
+    NB_CUDA(ctx, cudaHostAlloc((void**)&st->h_full_flag, sizeof(uint32_t), cudaHostAllocMapped));
+    *st->h_full_flag = 0u;
+    NB_CUDA(ctx, cudaHostGetDevicePointer((void**)&st->d_full_flag, st->h_full_flag, 0));
     NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->side_stream, cudaStreamNonBlocking));
     NB_CUDA(ctx, cudaEventCreateWithFlags(&st->fork_ev, cudaEventDisableTiming));
     NB_CUDA(ctx, cudaEventCreateWithFlags(&st->join_ev, cudaEventDisableTiming));
@@ -873,6 +975,17 @@ int ensure_state(nb_context* ctx, int n) {
     }
     st->cap = (int)cap;
     return NB_OK;
+}
+
+// once per evaluation, before run_build (and before the graph key is formed: the choice is part of it)
+void pick_sort_mode(nb_bh_state* st) {
+    static const bool env_full = getenv("NB_BH_FULL_SORT") != nullptr;   // measurement switch: eight plain passes
+    if (*reinterpret_cast<volatile uint32_t*>(st->h_full_flag)) {
+        *st->h_full_flag = 0u;
+        st->full_sort_left = 64;
+    }
+    st->sort_full = env_full || st->full_sort_left > 0;
+    if (st->full_sort_left > 0) st->full_sort_left--;
 }
 
 // stages: 1 = bounds, 2 = keys, 3 = sorts, 4 = tree
@@ -890,7 +1003,7 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
         // one memset clears the digit histograms, the tile tickets and the look-back status words of all 12 passes
         const int tiles = (n + SORT_TILE - 1) / SORT_TILE;
         st->os_stride = (size_t)tiles * 256;   // compact for this n, so that the words to clear are contiguous
-        NB_CUDA(ctx, cudaMemsetAsync(st->ghist, 0, ((size_t)N_DIGITS * 256 + 64 + N_DIGITS * st->os_stride) * sizeof(uint32_t),
+        NB_CUDA(ctx, cudaMemsetAsync(st->ghist, 0, ((size_t)N_DIGITS * 256 + 64 + N_SLOTS * st->os_stride) * sizeof(uint32_t),
                                      stream));
         keys_kernel<<<(n + KEYS_PER_BLOCK - 1) / KEYS_PER_BLOCK, KEYS_THREADS, 0, stream>>>(pos, n, st->bounds, st->key32[0],
                                                                                           st->key64[0], st->ghist);
@@ -904,14 +1017,30 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
             NB_CUDA(ctx, cudaStreamWaitEvent(st->side_stream, st->fork_ev, 0));
             sfc_stream = st->side_stream;
         }
-        rc = radix_sort<uint32_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key32, st->idx32, n, 32, 0,
-                                  &st->sfc_sel, sfc_stream);
+        rc = radix_sort<uint32_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key32, st->idx32, n, 0, 32, 0, 0,
+                                  true, 0, nullptr, &st->sfc_sel, sfc_stream);
         if (fork) {   // recorded even after a failed launch, so that a capture in progress can still be joined
             cudaEventRecord(st->join_ev, st->side_stream);
         }
         if (rc) { if (fork) cudaStreamWaitEvent(stream, st->join_ev, 0); return rc; }
-        rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n, 64, 4,
-                                  &st->tree_sel, stream);
+        if (st->sort_full) {
+            rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n, 0, 64,
+                                      4, 4, true, 0, nullptr, &st->tree_sel, stream);
+        } else {
+            uint32_t* const fix_count = st->os_ticket + FIX_COUNT_WORD;
+            uint32_t* const fix_flag = st->os_ticket + FIX_FLAG_WORD;
+            int sel = 0;
+            rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n,
+                                      HYBRID_LOW_BITS, 64, 4, 4 + HYBRID_LOW_BITS / 8, true, 0, nullptr, &sel, stream);
+            if (!rc) {
+                mark_runs_kernel<<<(n + 255) / 256, 256, 0, stream>>>(st->key64[sel], n, st->fix_work, fix_count, fix_flag);
+                fix_runs_kernel<<<1, 1024, 0, stream>>>(st->key64[sel], st->idx64[sel], st->fix_work, fix_count, fix_flag,
+                                                        st->d_full_flag);
+                rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n, 0,
+                                          64, 4, N_DIGITS, false, sel, fix_flag, &sel, stream);
+            }
+            st->tree_sel = sel;
+        }
         if (rc) { if (fork) cudaStreamWaitEvent(stream, st->join_ev, 0); return rc; }
     }
     if (upto >= 4 && n >= 2) {
@@ -1015,17 +1144,18 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
     static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 262144; }();
     const bool counting = (flags & NB_BH_COUNT_FLAG) != 0;
+    rc = ensure_state(ctx, n);   // allocation must not happen inside a capture
+    if (rc) return rc;
+    pick_sort_mode(ctx->bh);
     if (n > graph_max_n || n < 2 || counting) {
         rc = run_build(ctx, pos, n, flags, 4, theta, (cudaStream_t)stream);
         if (rc) return rc;
         return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, counting, (cudaStream_t)stream);
     }
     // launch-bound sizes: replay a captured graph of the same evaluation
-    rc = ensure_state(ctx, n);   // allocation must not happen inside a capture
-    if (rc) return rc;
     nb_bh_state* st = ctx->bh;
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
-    const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening};
+    const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening, st->sort_full};
     if (!st->graph_exec || !(st->graph_key == key)) {
         if (st->graph_exec) { cudaGraphExecDestroy(st->graph_exec); st->graph_exec = nullptr; }
         if (!st->capture_stream) NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->capture_stream, cudaStreamNonBlocking));

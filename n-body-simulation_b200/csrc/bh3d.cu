@@ -653,8 +653,8 @@ int run_build3(nb_context* ctx, const float* pos_, int n, int upto, float theta,
         keys3_kernel<<<(n + KEYS3_PER_BLOCK - 1) / KEYS3_PER_BLOCK, KEYS3_THREADS, 0, stream>>>(pos, n, st->bounds, st->key[0], st->ghist);
     }
     if (upto >= 3) {
-        rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key, st->idx, n, 64, 0, &st->sel,
-                                  stream);
+        rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key, st->idx, n, 0, 64, 0, 0,
+                                  true, 0, nullptr, &st->sel, stream);
         if (rc) return rc;
     }
     if (upto >= 4 && n >= 2) {

@@ -31,8 +31,10 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
                                                                const int32_t* __restrict__ vals_in,   // null: identity
                                                                int n, int shift, const uint32_t* __restrict__ ghist,
                                                                uint32_t* status, unsigned int* ticket,
-                                                               K* __restrict__ keys_out, int32_t* __restrict__ vals_out) {
+                                                               K* __restrict__ keys_out, int32_t* __restrict__ vals_out,
+                                                               const uint32_t* __restrict__ enable /* null: always */) {
     static_assert(SORT_THREADS == 256, "one thread per digit");
+    if (enable && *enable == 0u) return;   // a pass of the conditional full re-sort that is not needed
     constexpr int WARPS = SORT_THREADS / 32;
     constexpr unsigned FULLM = 0xffffffffu;
     __shared__ uint32_t cnt[WARPS][256];   // per warp and digit: count, then exclusive offset inside the tile's digit bin
@@ -160,16 +162,23 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const K* __restr
     }
 }
 
-// `digit0`: index of this sort's first digit in the [12][256] histogram / status layout.
+// Passes over the key bits [shift_begin, shift_end).  `hist0` is the index, in the [..][256] global histogram layout,
+// of the histogram of the key's LOWEST digit; `slot0` the index of the first pass's ticket and look-back status
+// area (every pass of an evaluation needs its own).  `sel_in` says which buffer holds the input; the first pass
+// takes the identity permutation as values when `identity` is set.  `enable` (device flag, may be null) turns
+// every pass into a no-op while it reads 0.
 template <typename K>
 int radix_sort(nb_context* ctx, uint32_t* ghist, uint32_t* os_status, size_t os_stride, unsigned int* os_ticket, K* keys[2],
-               int32_t* vals[2], int n, int bits, int digit0, int* sel_out, cudaStream_t stream) {
+               int32_t* vals[2], int n, int shift_begin, int shift_end, int hist0, int slot0, bool identity, int sel_in,
+               const uint32_t* enable, int* sel_out, cudaStream_t stream) {
     const int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
-    int sel = 0;
-    for (int shift = 0, d = digit0; shift < bits; shift += 8, d++) {
-        onesweep_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], shift == 0 ? nullptr : vals[sel], n, shift,
-                                                                ghist + 256 * d, os_status + (size_t)d * os_stride,
-                                                                os_ticket + d, keys[sel ^ 1], vals[sel ^ 1]);
+    int sel = sel_in, slot = slot0;
+    for (int shift = shift_begin; shift < shift_end; shift += 8, slot++) {
+        const bool first = identity && shift == shift_begin;
+        onesweep_kernel<K><<<nblocks, SORT_THREADS, 0, stream>>>(keys[sel], first ? nullptr : vals[sel], n, shift,
+                                                                ghist + 256 * (hist0 + shift / 8),
+                                                                os_status + (size_t)slot * os_stride, os_ticket + slot,
+                                                                keys[sel ^ 1], vals[sel ^ 1], enable);
         sel ^= 1;
     }
     *sel_out = sel;

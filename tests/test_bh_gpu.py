@@ -9,7 +9,7 @@ EPS = 1.01
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CASES = ["disk_8192", "disk_5000_ragged", "clustered_8192", "tight_clusters_4097", "duplicates_3000",
          "two_galaxies_6000", "tiny_2", "tiny_3", "tiny_33",
-         "all_coincident_700", "collinear_1500", "massless_half_2048", "far_offset_4096", "all_at_origin_100"]
+         "all_coincident_700", "collinear_1500", "massless_half_2048", "far_offset_4096", "all_at_origin_100", "small_knot_300", "dense_knot_6000"]
 
 
 def _cases(pkg):
@@ -25,7 +25,13 @@ def _cases(pkg):
     far = pkg.ics.uniform_disk(4096, seed=39)
     far[:, 0] += 3.0e6                        # ~0.25 resolution in x: many bodies share an x coordinate
     far[:, 1] -= 7.0e5
+    rng = np.random.default_rng(40)
+    knot = pkg.ics.uniform_disk(9000, seed=41)          # 300 bodies inside one level-20 cell: the sort's fix-up block
+    knot[5000:5300, :2] = knot[4999, :2] + rng.uniform(-4e-3, 4e-3, (300, 2)).astype(np.float32)
+    dense = pkg.ics.uniform_disk(20000, seed=42)        # 6000 of them: beyond the fix-up, the conditional full sort
+    dense[7000:13000, :2] = dense[6999, :2] + rng.uniform(-4e-3, 4e-3, (6000, 2)).astype(np.float32)
     return {
+        "small_knot_300": knot, "dense_knot_6000": dense,
         "all_at_origin_100": np.tile(np.array([[0.0, 0.0, 0.0, 5.0]], np.float32), (100, 1)),   # zero-extent box
         "all_coincident_700": same, "collinear_1500": line, "massless_half_2048": light, "far_offset_4096": far,
         "disk_8192": pkg.ics.uniform_disk(8192, seed=1),
@@ -283,3 +289,29 @@ def test_call_sequence_keeps_no_stale_state(pkg):
             st = eng.bh_stages(pos)
             assert np.all(np.diff(st["keys"][st["sorted_idx"]].astype(np.int64)) >= 0)
     eng.close()
+
+
+def test_dense_system_same_result_on_every_sort_path(pkg):
+    """A system with thousands of bodies inside one level-20 cell overflows the five-pass sort's repair block: the
+    first evaluation takes the conditional full sort on the device, the following ones are asked for eight plain
+    passes by the host.  Every path must give the same tree and the same accelerations, at a graph-replayed size and
+    at a plainly launched one."""
+    import torch
+    for n in (20000, 300000):
+        rng = np.random.default_rng(n)
+        pos_h = pkg.ics.uniform_disk(n, seed=43)
+        pos_h[7000:13000, :2] = pos_h[6999, :2] + rng.uniform(-4e-3, 4e-3, (6000, 2)).astype(np.float32)
+        pos = _dev(pos_h)
+        eng = pkg.Engine(0, n)
+        first, first_tree = None, None
+        for rep in range(4):
+            acc = torch.zeros(n, 4, device="cuda")
+            eng.bh_accel(pos, acc, 0.5, EPS)
+            torch.cuda.synchronize()
+            tree = eng.bh_export_tree()
+            if first is None:
+                first, first_tree = acc, tree
+            else:
+                assert torch.equal(acc, first), rep
+                assert all(np.array_equal(tree[k], first_tree[k]) for k in ("prefix", "level", "count"))
+        eng.close()
