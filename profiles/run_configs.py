@@ -70,6 +70,8 @@ def reference_force(n, pos_h, method, dim, theta, reps):
 
 
 configs = [
+    # the one timing the reference publishes (src/main.cu:11-19,53): 19.3 ms per tick on an unnamed GPU, with file output
+    ("0 main.cu workload: Barnes-Hut N=32768 theta=0.04, symplectic Euler DK", 32768, "disk", "bh", "Euler_Symplectic_DK", 2, 0.04, 100),
     ("1 direct N=16384 uniform disk, Leapfrog", 16384, "disk", "direct", "Verlet_DKD", 2, 0.5, 100),
     ("2 direct N=1048576, Leapfrog (1 GPU)", 1 << 20, "disk", "direct", "Verlet_DKD", 2, 0.5, 3),
     ("3 Barnes-Hut N=1048576 theta=0.5, Leapfrog", 1 << 20, "disk", "bh", "Verlet_DKD", 2, 0.5, 20),
