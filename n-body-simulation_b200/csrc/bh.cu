@@ -668,7 +668,11 @@ constexpr int WL_WARPS = 4;
 constexpr int WL_QCAP = 1024;   // node ids per group (measured peak at N = 1M, theta = 0.5: see bench counters)
 constexpr int WL_LCAP = 64;     // pending accepted records per group
 
-template <bool COUNT>
+// SPLIT > 1 (small systems, where one warp per group leaves most of the machine idle): SPLIT warps of a block share
+// one group.  They walk the top of the tree in lockstep until the queue holds 8 * SPLIT nodes, then each keeps every
+// SPLIT-th node (the others discard what they summed so far) and walks its share; the partial sums are added in
+// warp order, so the result stays deterministic.
+template <bool COUNT, int SPLIT>
 __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const float4* __restrict__ pos,
                                                                   const int32_t* __restrict__ sorted_idx, int n,
                                                                   const float4* __restrict__ cblk,
@@ -683,10 +687,17 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
     __shared__ float2 lm_s[WL_WARPS][WL_LCAP / 2];
     __shared__ float4 amb_s[WL_WARPS][32];   // undecided records of the current batch
     __shared__ float2 wit_s[WL_WARPS][4];
+    __shared__ float2 part_s[SPLIT > 1 ? WL_WARPS : 1][32];
+    static_assert(SPLIT == 1 || SPLIT == 2 || SPLIT == 4, "SPLIT warps of one block share a group");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned FULLM = 0xffffffffu;
-    const int g = blockIdx.x * WL_WARPS + warp;
-    if (g >= group_count) return;
+    const int g = (blockIdx.x * WL_WARPS + warp) / SPLIT;
+    const int sub = warp % SPLIT;
+    if (g >= group_count) {
+        if (SPLIT > 1) __syncthreads();   // pairs with the barrier before the partial sums are added
+        return;
+    }
+    bool lockstep = SPLIT > 1;
     const int bi = (group_begin + g) * 32 + lane;
     const bool valid = bi < n;
     // lanes past the end of the sorted order shadow the group's first target: they vote like it and store nothing
@@ -827,6 +838,24 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         qtop += nrej;
         __syncwarp();
         if (COUNT) c_depth = max(c_depth, qtop);
+        if (SPLIT > 1 && lockstep && (qtop >= 8 * SPLIT || qtop == 0)) {
+            // end of the common prefix: warp `sub` keeps queue entries sub, sub + SPLIT, ...; only warp 0 keeps the sums
+            lockstep = false;
+            if (sub != 0) {
+                ax = ay = 0.f;
+                AX2 = AY2 = 0ull;
+                lcount = 0;
+                if (COUNT) c_open = c_exam = c_inter = 0;
+            }
+            for (int base = 0; base < qtop; base += 32) {
+                const int j = base + lane;
+                const uint32_t e = j < qtop ? q[j] : 0u;
+                __syncwarp();
+                if (j < qtop && j % SPLIT == sub) q[j / SPLIT] = e;
+                __syncwarp();
+            }
+            qtop = (qtop - sub + SPLIT - 1) / SPLIT;
+        }
         if (qtop == 0) break;
         // ---- pop up to eight nodes: lane l takes child (l & 3) of the (l >> 2)-th node from the top ----------
         const int k = min(8, qtop);
@@ -866,7 +895,20 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         ax += a0 + a1;
         ay += b0 + b1;
     }
-    if (valid) acc[body] = make_float4(ax, ay, 0.f, 0.f);
+    if (SPLIT > 1) {
+        if (lockstep && sub != 0) ax = ay = 0.f;   // left the loop inside the common prefix (queue overflow)
+        if (sub != 0) part_s[warp][lane] = make_float2(ax, ay);
+        __syncthreads();
+        if (sub == 0) {
+#pragma unroll
+            for (int w = 1; w < SPLIT; w++) {
+                const float2 p = part_s[warp + w][lane];
+                ax += p.x;
+                ay += p.y;
+            }
+        }
+    }
+    if (valid && sub == 0) acc[body] = make_float4(ax, ay, 0.f, 0.f);
     if (overflow && lane == 0) atomicOr(&counters[4], 1ull);
     if (COUNT && lane == 0) {
         atomicAdd(&counters[0], c_open);
@@ -1095,14 +1137,23 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
             walk_kernel<false><<<blocks, WALK_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, st->clink, st->spos,
                                                                       st->root_rec, eps, group_begin, group_count, acc, st->counters);
     } else {
-        const int blocks = (group_count + WL_WARPS - 1) / WL_WARPS;
+        // fewer groups than it takes to keep the SMs busy (16 warps each): 2 or 4 warps share a group
+        static const int forced_split = [] { const char* v = getenv("NB_BH_WALK_SPLIT"); return v ? atoi(v) : 0; }();
+        const int busy = ctx->sm_count * 16;
+        int split = group_count >= busy ? 1 : (2 * group_count >= busy ? 2 : 4);
+        if (forced_split == 1 || forced_split == 2 || forced_split == 4) split = forced_split;
+        const int blocks = (group_count * split + WL_WARPS - 1) / WL_WARPS;
         const uint32_t* links = reinterpret_cast<const uint32_t*>(st->clink);
-        if (count)
-            walk_lists_kernel<true><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, st->spos,
-                                                                         st->root_rec, eps, group_begin, group_count, acc, st->counters);
-        else
-            walk_lists_kernel<false><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, st->spos,
-                                                                          st->root_rec, eps, group_begin, group_count, acc, st->counters);
+#define NB_LAUNCH_WALK(COUNTING, SPLIT)                                                                               \
+    walk_lists_kernel<COUNTING, SPLIT><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, \
+                                                                            st->spos, st->root_rec, eps, group_begin,         \
+                                                                            group_count, acc, st->counters)
+        if (count) {
+            if (split == 1) NB_LAUNCH_WALK(true, 1); else if (split == 2) NB_LAUNCH_WALK(true, 2); else NB_LAUNCH_WALK(true, 4);
+        } else {
+            if (split == 1) NB_LAUNCH_WALK(false, 1); else if (split == 2) NB_LAUNCH_WALK(false, 2); else NB_LAUNCH_WALK(false, 4);
+        }
+#undef NB_LAUNCH_WALK
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
