@@ -40,7 +40,12 @@ extern "C" {
 #define NB_OK 0
 #define NB_ERR_INVALID 1   /* bad argument */
 #define NB_ERR_CUDA 2      /* a CUDA runtime call failed; see nb_last_error */
-#define NB_ERR_OVERFLOW 3  /* a device-side capacity was exceeded (tree node pool, traversal stack) */
+#define NB_ERR_OVERFLOW 3  /* reserved.  No entry point returns it today: the capacities the reference can exceed silently
+                              (node pool src/BarnesHutKernels.cu:308-311, 64-entry stack :388) cannot be exceeded here --
+                              the tree has at most n-1 nodes by construction, cells at the 32-level depth cap become
+                              buckets, and a walk whose node queue fills up finishes its group depth-first in bounded
+                              space (status bit 0 of nb_bh_last_counters reports that this happened; the result is
+                              the same accepted set) */
 #define NB_ERR_NO_DEVICE 4
 #define NB_ERR_TOO_LARGE 5  /* problem size beyond a fixed capacity (nb_direct_accel_noalloc) */
 
@@ -49,6 +54,9 @@ extern "C" {
 #define NB_DIRECT_ORDERED 1   /* one accumulator per target, sources summed in index order 0..n-1: the
                                  summation order of src/DirectComputeKernels.cu:16-30,52-68, bit-identical
                                  to the reference kernel's output */
+#define NB_DIRECT_NO_HOIST 2  /* keep the 12-operation arithmetic for every source tile: never take a common mass out
+                                 of the sum (the default does so for tiles of 1024 equal masses -- same summation order,
+                                 one extra rounding, 11 operations) */
 
 /* flags for nb_bh_accel* */
 #define NB_BH_FRESH_BOUNDS 0       /* bounding box recomputed from scratch every call (fix) */
@@ -62,15 +70,17 @@ typedef struct nb_context nb_context;
 
 /* ---- lifetime ------------------------------------------------------------------------------------ */
 
-/* Creates an engine bound to CUDA device `device`.  `max_bodies` sizes the scratch memory up front
- * (it grows on demand if a later call passes more bodies).  Replaces the cudaMalloc block of
- * BarnesHut::setSystem (src/ComputeMethods.cpp:40-44). */
+/* Creates an engine bound to CUDA device `device`.  Replaces the cudaMalloc block of BarnesHut::setSystem
+ * (src/ComputeMethods.cpp:40-44).  Scratch memory is allocated by the FIRST call of each path (direct: tile flags and,
+ * when the source range is split, partial sums; Barnes-Hut: keys, tree, prefix sums, sized for max(max_bodies, n)) and
+ * grows -- behind a device synchronisation -- only when a later call passes more bodies than any before it; steady-state
+ * calls allocate nothing.  Make the first call of a path outside any stream capture. */
 int nb_create(nb_context** out, int device, int max_bodies);
 int nb_destroy(nb_context* ctx);
 /* Human-readable description of the last failure on this handle (or of the last failed nb_create when
  * ctx is NULL).  Replaces the printf(cudaGetErrorString()) pattern of src/BarnesHutKernels.cu:15-17. */
 const char* nb_last_error(const nb_context* ctx);
-/* Device the handle is bound to, number of SMs, and bytes of scratch currently held. */
+/* Device the handle is bound to, number of SMs, and bytes of device scratch currently held (all paths). */
 int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* scratch_bytes);
 
 /* ---- direct all-pairs ---------------------------------------------------------------------------- */
@@ -143,9 +153,17 @@ int nb_bh_stages_host(nb_context* ctx, const float* pos, int n, int flags, float
 int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* level, int32_t* count,
                       double* mass, double* cx, double* cy);
 
-/* Counters of the last walk: nodes opened, children examined, lane interactions, max stack depth, nodes
- * in the tree, status flags (bit 0 = stack overflow). */
+/* Counters of the last walk: nodes opened, children examined, lane interactions, max queue depth, nodes
+ * in the tree, status flags (bit 0 = at least one group's node queue filled up and that group finished its walk in
+ * depth-first order -- slower, same result; the counters [0..3] need NB_BH_COUNT_WALK, the status bit does not). */
 int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]);
+
+/* Facts about the tree built by the last nb_bh_* call (synchronises; tests and profiling): info[0] = nodes,
+ * info[1] = bodies the five-pass tree-key sort left to its repair block (runs sharing the upper 40 key bits),
+ * info[2] = bit 0: the repair block overflowed and the conditional full sort ran on the device, bit 1: the host had
+ * already asked for eight plain passes, info[3] = deepest level at which a node splits (32 = depth-cap buckets exist).
+ * The reference prints nothing comparable; its node pool overflow message is src/BarnesHutKernels.cu:308-311. */
+int nb_bh_build_info(nb_context* ctx, int64_t info[4]);
 
 /* ---- Barnes-Hut in 3D (octree) -------------------------------------------------------------------- */
 
@@ -207,6 +225,50 @@ int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const floa
 int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, const float* acc, const float* acc_prev, int begin,
                          int count, float dt, int kick_kind, double kick_coef, int drift_kind, double drift_coef,
                          void* stream);
+
+/* ---- one stepper sub-step around the Barnes-Hut force, fused ----------------------
+ *
+ * Every stepper of the reference except Velocity Verlet is a pre-force drift followed by one or more
+ * [force evaluation; kick; drift] groups (src/IntegrationMethods.cu:26-35 KD, :58-67 DK, :96-105 Verlet DKD,
+ * :245-270 Forest-Ruth, :343-374 PEFRL).  nb_bh_step_groups runs ONE such group -- optional drift of all bodies, tree
+ * build, walk of the groups [group_begin, group_begin + group_count) of the sorted order, and the kick + drift of the
+ * walked bodies in the walk's epilogue, where the acceleration is still in registers -- with the reference's mixed
+ * FP32/FP64 arithmetic (the kinds of nb_integrate_substep; NB_KICK_MEAN_F64 and NB_DRIFT_VV_F64 are not available
+ * here).  No counterpart in the reference, which launches separate kernels on one GPU.
+ *
+ *   pos, vel : device float4[n] in body order, read AND written.
+ *   rows_out == NULL (one GPU): pos[b], vel[b] of every walked body are updated in place; acc_out (device float4[n], may
+ *       be NULL) also receives the accelerations.
+ *   rows_out != NULL (sharded): pos/vel of the walked bodies are NOT updated; instead row (s - 32 group_begin) of
+ *       rows_out (device float4[32 group_count]) receives (x', y', vx', vy') of the body in sorted slot s.  The caller
+ *       all-gathers the rows of all ranks into one float4[n] array in sorted order and hands it to the NEXT call as
+ *       rows_in (with the drift kind of THIS call as prev_drift_*): that call first scatters the rows back to body order
+ *       (it still holds this call's permutation), applies the same drift to z (a_z = 0 in the 2D path, so v_z never
+ *       changes), then its own pre-force drift.  Every rank does that for all n bodies, so positions and velocities stay
+ *       replicated and bit-identical on all ranks with ONE collective per force evaluation (16 bytes per body) instead
+ *       of an all-gather of positions plus an exchange of accelerations.  A last call with group_count = 0 and
+ *       kick = drift = none brings pos/vel up to date.
+ *   stats_out (device double[2 ceil(n/32)], may be NULL): per walked group g, [2g] = sum m|v| and [2g+1] = sum m v^2/2
+ *       of the kicked velocities, lanes added in a fixed order -- the two sums of SimulationStats::computeStats
+ *       (src/SimulationStats.cu:29-44) without a second pass over the bodies. */
+typedef struct nb_bh_step {
+    float theta, softening, dt;
+    int flags;                 /* NB_BH_FRESH_BOUNDS / NB_BH_ACCUMULATE_BOUNDS */
+    int group_begin, group_count;
+    int pre_drift_kind;        /* NB_DRIFT_*: drift of ALL bodies before the force (NB_DRIFT_NONE: none) */
+    double pre_drift_coef;
+    int kick_kind;             /* NB_KICK_*: after the force, walked bodies only */
+    double kick_coef;
+    int drift_kind;            /* NB_DRIFT_*: after the kick, walked bodies only */
+    double drift_coef;
+    const float* rows_in;      /* sharded: all-gathered rows of the previous call, or NULL */
+    int prev_drift_kind;       /* the drift_kind / drift_coef of the call that produced rows_in */
+    double prev_drift_coef;
+    float* rows_out;           /* sharded: this rank's rows; NULL = update pos/vel in place */
+    float* acc_out;            /* in-place mode only, may be NULL */
+    double* stats_out;         /* may be NULL */
+} nb_bh_step;
+int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_bh_step* step, void* stream);
 
 /* ---- diagnostics (callers of the path) ------------------------------------- */
 

@@ -16,7 +16,7 @@ _LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
 _lib = None
 
 NB_OK = 0
-NB_DIRECT_AUTO, NB_DIRECT_ORDERED = 0, 1
+NB_DIRECT_AUTO, NB_DIRECT_ORDERED, NB_DIRECT_NO_HOIST = 0, 1, 2
 NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS, NB_BH_COUNT_WALK = 0, 1, 0x100
 
 # every symbol include/nbody_b200.h declares (tests check that the library exports each one)
@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_accel_noalloc",
     "nb_direct_last_launch",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
-    "nb_bh_last_counters", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
+    "nb_bh_last_counters", "nb_bh_build_info", "nb_bh_step_groups", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
     "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities",
     "nb_bh3d_accel", "nb_bh3d_accel_groups", "nb_bh3d_stages_host", "nb_bh3d_export_tree", "nb_bh3d_last_counters",
 ]
@@ -33,6 +33,17 @@ ABI_SYMBOLS = [
 
 class NbodyError(RuntimeError):
     pass
+
+
+class BHStep(C.Structure):
+    """struct nb_bh_step of include/nbody_b200.h."""
+    _fields_ = [("theta", C.c_float), ("softening", C.c_float), ("dt", C.c_float), ("flags", C.c_int),
+                ("group_begin", C.c_int), ("group_count", C.c_int),
+                ("pre_drift_kind", C.c_int), ("pre_drift_coef", C.c_double),
+                ("kick_kind", C.c_int), ("kick_coef", C.c_double),
+                ("drift_kind", C.c_int), ("drift_coef", C.c_double),
+                ("rows_in", C.c_void_p), ("prev_drift_kind", C.c_int), ("prev_drift_coef", C.c_double),
+                ("rows_out", C.c_void_p), ("acc_out", C.c_void_p), ("stats_out", C.c_void_p)]
 
 
 def library_path():
@@ -63,6 +74,8 @@ def lib():
         L.nb_bh_stages_host.argtypes = [vp, vp, i, i, vp, vp, vp, vp]
         L.nb_bh_export_tree.argtypes = [vp, C.POINTER(i), vp, vp, vp, vp, vp, vp]
         L.nb_bh_last_counters.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.nb_bh_build_info.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.nb_bh_step_groups.argtypes = [vp, vp, vp, i, C.POINTER(BHStep), vp]
         L.nb_bh3d_accel.argtypes = [vp, vp, vp, i, f, f, i, vp]
         L.nb_bh3d_accel_groups.argtypes = [vp, vp, vp, i, f, f, i, i, i, vp]
         L.nb_bh3d_stages_host.argtypes = [vp, vp, i, vp, vp, vp]
@@ -198,6 +211,27 @@ class Engine:
         c = (C.c_int64 * 6)()
         self._check(lib().nb_bh_last_counters(self._h, c), "nb_bh_last_counters")
         return dict(opened=c[0], examined=c[1], interactions=c[2], max_stack=c[3], nodes=c[4], status=c[5])
+
+    def bh_step_groups(self, pos, vel, theta, softening, dt, group_begin, group_count, pre_drift=(0, 0.0), kick=(0, 0.0),
+                       drift=(0, 0.0), rows_in=None, prev_drift=(0, 0.0), rows_out=None, acc_out=None, stats_out=None,
+                       flags=NB_BH_FRESH_BOUNDS, stream=None):
+        """One [pre-drift; force; kick; drift] group of a stepper with the kick and drift fused into the walk
+        (nb_bh_step_groups).  pos, vel: CUDA float32 [n,4], updated in place unless rows_out is given."""
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(vel, n)
+        st = BHStep(theta, softening, dt, flags, group_begin, group_count, pre_drift[0], pre_drift[1], kick[0], kick[1],
+                    drift[0], drift[1], rows_in.data_ptr() if rows_in is not None else None, prev_drift[0], prev_drift[1],
+                    rows_out.data_ptr() if rows_out is not None else None,
+                    acc_out.data_ptr() if acc_out is not None else None,
+                    stats_out.data_ptr() if stats_out is not None else None)
+        self._check(lib().nb_bh_step_groups(self._h, pos.data_ptr(), vel.data_ptr(), n, C.byref(st), _stream_ptr(stream)),
+                    "nb_bh_step_groups")
+
+    def bh_build_info(self):
+        c = (C.c_int64 * 4)()
+        self._check(lib().nb_bh_build_info(self._h, c), "nb_bh_build_info")
+        return dict(nodes=c[0], repaired=c[1], full_sort_on_device=bool(c[2] & 1), full_sort_by_host=bool(c[2] & 2),
+                    deepest_level=c[3])
 
     # -- Leapfrog (Verlet_DKD) kick/drift on a slice ---------------------------------------------------
     def verlet_dkd_drift(self, pos, vel, begin, count, dt, stream=None):

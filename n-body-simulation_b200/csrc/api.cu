@@ -60,7 +60,9 @@ int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* 
     if (!ctx) return NB_ERR_INVALID;
     if (device) *device = ctx->device;
     if (sm_count) *sm_count = ctx->sm_count;
-    if (scratch_bytes) *scratch_bytes = ctx->tile_flags_bytes + ctx->partial_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes;
+    if (scratch_bytes)
+        *scratch_bytes = ctx->tile_flags_bytes + ctx->partial_bytes + ctx->stats_bytes + ctx->dev_pos_bytes + ctx->dev_acc_bytes +
+                         ctx->bh_bytes + ctx->bh3_bytes;
     return NB_OK;
 }
 

@@ -20,6 +20,7 @@
 //     opened, bodies are always summed (src/BarnesHutKernels.cu:398-445), same LIFO order, same FP32
 //     arithmetic per interaction.
 #include "common.cuh"
+#include "integrate.cuh"
 
 #include <algorithm>
 #include <cfloat>
@@ -81,16 +82,18 @@ struct nb_bh_state {
     float4* root_rec = nullptr;        // the root cell as a child record (cx, cy, m, link)
     unsigned long long* counters = nullptr;  // opened, examined, interactions, max stack, overflow flag
     int last_n = 0;
+    bool perm_valid = false;   // the SFC permutation of the last evaluation is intact (nb_bh_step_groups: rows_in)
     // result locations of the last sorts
     int sfc_sel = 0, tree_sel = 0;
     // small systems are launch-bound (20 launches + 1 memset per evaluation): the whole evaluation is captured once
     // into a CUDA graph and replayed while the call's arguments stay the same
     struct GraphKey {
         const float* pos; float* acc; int n, flags, group_begin, group_count, accumulate; float theta, eps; bool sort_full;
+        int qcap;
         bool operator==(const GraphKey& o) const {
             return pos == o.pos && acc == o.acc && n == o.n && flags == o.flags && group_begin == o.group_begin &&
                    group_count == o.group_count && accumulate == o.accumulate && theta == o.theta && eps == o.eps &&
-                   sort_full == o.sort_full;
+                   sort_full == o.sort_full && qcap == o.qcap;
         }
     };
     GraphKey graph_key{};
@@ -104,14 +107,72 @@ struct nb_bh_state {
 
 namespace {
 
+// What the first kernel of an evaluation does to the bodies before it measures the box (nb_bh_step_groups):
+//   mode 0  nothing (plain force evaluation);
+//   mode 1  the stepper's pre-force drift, in place, on all n bodies (one GPU);
+//   mode 2  sharded run: `rows` holds (x', y', vx', vy') of every body after the previous evaluation's kick + drift, in
+//           THAT evaluation's sorted order (`perm`: body of each sorted slot), as all-gathered from the ranks that walked
+//           them; they are scattered back to body order, z takes the same drift (its velocity never changes in the 2D
+//           path: a_z = 0), then the pre-force drift.  Every rank does this for all n bodies and ends up with the same
+//           replicated state.
+struct PrepArgs {
+    int mode;
+    float4* pos_rw;
+    float4* vel_rw;
+    const float4* rows;
+    const int32_t* perm;
+    SubstepArgs post;   // mode 2: drift of the previous evaluation's epilogue (applied to z here)
+    SubstepArgs pre;    // modes 1, 2: drift before this evaluation (NB_DRIFT_NONE: none)
+};
+
+// What the walk does with a target's acceleration (nb_bh_step_groups): the kick and drift that follow the force
+// evaluation in the reference's steppers (src/IntegrationMethods.cu:81-93 and the other K+D kernels) run in the walk's
+// epilogue, where the acceleration still sits in registers.
+//   mode 0  acc[body] = a;
+//   mode 1  vel[body], pos[body] updated in place (one GPU);
+//   mode 2  rows[sorted slot - row_base] = (x', y', vx', vy') -- the rank's contribution to the all-gather.
+// `stats` (optional): per group, sum m|v| and sum m v^2 / 2 of the kicked velocities (src/SimulationStats.cu:29-44).
+struct WalkEpilogue {
+    int mode;
+    float4* pos_rw;
+    float4* vel_rw;
+    float4* rows;
+    int row_base;
+    SubstepArgs s;
+    double* stats;
+};
+
 // ------------------------------------------------------------------------------------------------------
 // bounds: global min/max of x and y, padded by 0.1 % of |coord|   (src/BarnesHutKernels.cu:152-195)
 // ------------------------------------------------------------------------------------------------------
 __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* part,
-                              unsigned int* __restrict__ ticket, float4* __restrict__ bounds, int accumulate) {
+                              unsigned int* __restrict__ ticket, float4* __restrict__ bounds, int accumulate,
+                              unsigned long long* __restrict__ walk_status, const PrepArgs prep) {
     float mnx = FLT_MAX, mny = FLT_MAX, mxx = -FLT_MAX, mxy = -FLT_MAX;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 p = pos[i];
+        float4 p;
+        if (prep.mode == 0) {
+            p = pos[i];
+        } else if (prep.mode == 1) {
+            p = prep.pos_rw[i];
+            const float4 v = prep.vel_rw[i];
+            p.x = drift1g(prep.pre, p.x, v.x, 0.f);
+            p.y = drift1g(prep.pre, p.y, v.y, 0.f);
+            p.z = drift1g(prep.pre, p.z, v.z, 0.f);
+            prep.pos_rw[i] = p;
+        } else {
+            const int body = prep.perm[i];
+            const float4 r = prep.rows[i];
+            p = prep.pos_rw[body];
+            float4 v = prep.vel_rw[body];
+            p.x = r.x; p.y = r.y; v.x = r.z; v.y = r.w;
+            p.z = drift1g(prep.post, p.z, v.z, 0.f);
+            p.x = drift1g(prep.pre, p.x, v.x, 0.f);
+            p.y = drift1g(prep.pre, p.y, v.y, 0.f);
+            p.z = drift1g(prep.pre, p.z, v.z, 0.f);
+            prep.pos_rw[body] = p;
+            prep.vel_rw[body] = v;
+        }
         mnx = fminf(mnx, p.x);
         mny = fminf(mny, p.y);
         mxx = fmaxf(mxx, p.x);
@@ -165,6 +226,7 @@ __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* par
         }
         *bounds = make_float4(b0, b1, b2, b3);
         *ticket = 0u;
+        *walk_status = 0ull;   // the status flags of nb_bh_last_counters describe THIS evaluation
     }
 }
 
@@ -667,6 +729,11 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
 constexpr int WL_WARPS = 4;
 constexpr int WL_QCAP = 1024;   // node ids per group (measured peak at N = 1M, theta = 0.5: see bench counters)
 constexpr int WL_LCAP = 64;     // pending accepted records per group
+// A group whose queue would pass `qcap` entries (default WL_QCAP - WL_DFS_ROOM) finishes depth-first instead: one
+// node per pop, all lanes voting on the same child, as walk_kernel does.  From any queue state that order adds at most
+// 3 entries per remaining tree level (3 * 32 = 96) on top of the batch being pushed (<= 32), so the array cannot
+// overflow and the accepted set is unchanged -- only the schedule and the order of the sum differ.
+constexpr int WL_DFS_ROOM = 128;
 
 // SPLIT > 1 (small systems, where one warp per group leaves most of the machine idle): SPLIT warps of a block share
 // one group.  They walk the top of the tree in lockstep until the queue holds 8 * SPLIT nodes, then each keeps every
@@ -680,7 +747,8 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
                                                                   const float4* __restrict__ spos,
                                                                   const float4* __restrict__ root_rec, float eps,
                                                                   int group_begin, int group_count, float4* __restrict__ acc,
-                                                                  unsigned long long* __restrict__ counters) {
+                                                                  unsigned long long* __restrict__ counters, int qcap,
+                                                                  const WalkEpilogue epi) {
     __shared__ uint32_t q_s[WL_WARPS][WL_QCAP];
     // pending accepted records, two per slot so that the evaluation runs on FP32x2: (cx0, cx1, cy0, cy1) and (m0, m1)
     __shared__ float4 lxy_s[WL_WARPS][WL_LCAP / 2];
@@ -734,7 +802,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
     int qtop = 0, lcount = 0;
     unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
     int c_depth = 0;
-    bool overflow = false;
+    bool depth_first = false;
 
     auto add = [&](float cx, float cy, float m) {
         const float dx = cx - x, dy = cy - y;
@@ -833,11 +901,51 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         if (accp) append(lcount + __popc(accm & below), rec.x, rec.y, rec.z);
         lcount += __popc(accm);
         const int nrej = __popc(rejm);
-        if (qtop + nrej > WL_QCAP) { overflow = true; break; }
+        if (qtop + nrej > qcap) depth_first = true;   // still room for this batch (WL_DFS_ROOM), none for the schedule
         if (rej) q[qtop + __popc(rejm & below)] = link;
         qtop += nrej;
         __syncwarp();
         if (COUNT) c_depth = max(c_depth, qtop);
+        if (depth_first) {
+            // the rest of this group's walk in depth-first order (src/BarnesHutKernels.cu:409-445): bounded queue growth
+            while (qtop > 0) {
+                const uint32_t ent = q[qtop - 1];
+                __syncwarp();
+                qtop--;
+                if (COUNT) c_open++;
+                const uint32_t id = ent & 0x7FFFFFFFu;
+                if (ent & LINK_BUCKET) {
+                    const float4 h = cblk[4 * (size_t)id];
+                    const int first = __float_as_int(h.x), cnt = __float_as_int(h.y);
+                    for (int t = 0; t < cnt; t++) {
+                        const float4 p = spos[first + t];
+                        add(p.x, p.y, p.z);
+                    }
+                    if (COUNT) { c_exam += cnt; c_inter += cnt; }
+                    continue;
+                }
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const float4 r4 = cblk[4 * (size_t)id + c];
+                    const uint32_t lk = clink[4 * (size_t)id + c];
+                    const float dx = r4.x - x, dy = r4.y - y;
+                    const float r = __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps));
+                    if (__all_sync(FULLM, r4.w <= r)) {
+                        const float kk = rcp_approx(r) * r4.z;
+                        ax = __fmaf_rn(kk, dx, ax);
+                        ay = __fmaf_rn(kk, dy, ay);
+                        if (COUNT && lk != LINK_EMPTY) { c_exam++; c_inter++; }
+                    } else {
+                        if (lane == 0) q[qtop] = lk;
+                        qtop++;
+                        if (COUNT) c_exam++;
+                    }
+                }
+                __syncwarp();
+                if (COUNT) c_depth = max(c_depth, qtop);
+            }
+            break;
+        }
         if (SPLIT > 1 && lockstep && (qtop >= 8 * SPLIT || qtop == 0)) {
             // end of the common prefix: warp `sub` keeps queue entries sub, sub + SPLIT, ...; only warp 0 keeps the sums
             lockstep = false;
@@ -896,7 +1004,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         ay += b0 + b1;
     }
     if (SPLIT > 1) {
-        if (lockstep && sub != 0) ax = ay = 0.f;   // left the loop inside the common prefix (queue overflow)
+        if (lockstep && sub != 0) ax = ay = 0.f;   // left the loop inside the common prefix (went depth-first there)
         if (sub != 0) part_s[warp][lane] = make_float2(ax, ay);
         __syncthreads();
         if (sub == 0) {
@@ -908,8 +1016,43 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
             }
         }
     }
-    if (valid && sub == 0) acc[body] = make_float4(ax, ay, 0.f, 0.f);
-    if (overflow && lane == 0) atomicOr(&counters[4], 1ull);
+    if (epi.mode == 0) {
+        if (valid && sub == 0) acc[body] = make_float4(ax, ay, 0.f, 0.f);
+    } else if (sub == 0) {
+        // the stepper's kick + drift on this target (a_z = 0 in the 2D path), src/IntegrationMethods.cu:81-93 and kin
+        float4 v = epi.vel_rw[body];
+        float4 p = epi.pos_rw[body];   // z and mass were not kept in registers through the walk
+        v.x = kick1(epi.s, v.x, ax, 0.f);
+        v.y = kick1(epi.s, v.y, ay, 0.f);
+        p.x = drift1g(epi.s, p.x, v.x, ax);
+        p.y = drift1g(epi.s, p.y, v.y, ay);
+        if (epi.mode == 1) {
+            v.z = kick1(epi.s, v.z, 0.f, 0.f);
+            p.z = drift1g(epi.s, p.z, v.z, 0.f);
+            if (valid) {
+                epi.vel_rw[body] = v;
+                epi.pos_rw[body] = p;
+            }
+            if (acc && valid) acc[body] = make_float4(ax, ay, 0.f, 0.f);
+        } else if (valid) {
+            epi.rows[bi - epi.row_base] = make_float4(p.x, p.y, v.x, v.y);
+        }
+        if (epi.stats) {   // SimulationStats "moment" and kinetic energy of the kicked velocities (R2 formula, :34-36)
+            double vv = sqrt((double)(v.x * v.x + v.y * v.y));
+            double lm = valid ? vv * (double)p.w : 0.0, lk = valid ? 0.5 * vv * vv * (double)p.w : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lm += __shfl_xor_sync(FULLM, lm, o);
+                lk += __shfl_xor_sync(FULLM, lk, o);
+            }
+            if (lane == 0) {
+                epi.stats[2 * (size_t)(group_begin + g)] = lm;
+                epi.stats[2 * (size_t)(group_begin + g) + 1] = lk;
+            }
+        }
+    }
+    if (depth_first && lane == 0) atomicOr(&counters[4], 1ull);   // informative: some group left the batched schedule
+    if (COUNT && SPLIT > 1 && lockstep && sub != 0) c_open = c_exam = c_inter = 0;   // a redundant copy of warp 0's walk
     if (COUNT && lane == 0) {
         atomicAdd(&counters[0], c_open);
         atomicAdd(&counters[1], c_exam);
@@ -923,9 +1066,35 @@ __global__ void zero_acc_kernel(float4* acc, int n) {
     if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+// a system of one body: zero acceleration, the epilogue still applies (the drift moves it)
+__global__ void lone_body_kernel(const float4* __restrict__ pos, float4* __restrict__ acc, const WalkEpilogue epi) {
+    if (threadIdx.x != 0) return;
+    float4 v = epi.vel_rw[0];
+    float4 p = pos[0];
+    v.x = kick1(epi.s, v.x, 0.f, 0.f);
+    v.y = kick1(epi.s, v.y, 0.f, 0.f);
+    p.x = drift1g(epi.s, p.x, v.x, 0.f);
+    p.y = drift1g(epi.s, p.y, v.y, 0.f);
+    if (epi.mode == 1) {
+        v.z = kick1(epi.s, v.z, 0.f, 0.f);
+        p.z = drift1g(epi.s, p.z, v.z, 0.f);
+        epi.vel_rw[0] = v;
+        epi.pos_rw[0] = p;
+        if (acc) acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+        epi.rows[0 - epi.row_base] = make_float4(p.x, p.y, v.x, v.y);
+    }
+    if (epi.stats) {
+        const double vv = sqrt((double)(v.x * v.x + v.y * v.y));
+        epi.stats[0] = vv * (double)p.w;
+        epi.stats[1] = 0.5 * vv * vv * (double)p.w;
+    }
+}
+
 template <typename T>
 int alloc(nb_context* ctx, T** p, size_t count) {
     NB_CUDA(ctx, cudaMalloc((void**)p, count * sizeof(T)));
+    ctx->bh_bytes += count * sizeof(T);
     return NB_OK;
 }
 
@@ -963,6 +1132,7 @@ int ensure_state(nb_context* ctx, int n) {
         free_state(ctx->bh);
         delete ctx->bh;
         ctx->bh = nullptr;
+        ctx->bh_bytes = 0;
     }
     nb_bh_state* st = new nb_bh_state();
     ctx->bh = st;
@@ -1031,7 +1201,8 @@ void pick_sort_mode(nb_bh_state* st) {
 }
 
 // stages: 1 = bounds, 2 = keys, 3 = sorts, 4 = tree
-int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, float theta, cudaStream_t stream) {
+int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, float theta, cudaStream_t stream,
+              const PrepArgs& prep = PrepArgs{}) {
     int rc = ensure_state(ctx, n);
     if (rc) return rc;
     nb_bh_state* st = ctx->bh;
@@ -1039,7 +1210,7 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
     st->last_n = n;
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
     int bblocks = std::min(1024, std::max(1, (n + 1023) / 1024));
-    bounds_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, accumulate);
+    bounds_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, accumulate, st->counters + 4, prep);
     st->bounds_valid = true;
     if (upto >= 2) {
         // one memset clears the digit histograms, the tile tickets and the look-back status words of all 12 passes
@@ -1116,17 +1287,26 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
     return NB_OK;
 }
 
+// NB_BH_WALK_QCAP (tests): a smaller queue threshold sends groups down the depth-first path early
+int walk_qcap() {
+    int qcap = WL_QCAP - WL_DFS_ROOM;
+    if (const char* v = getenv("NB_BH_WALK_QCAP")) qcap = std::max(0, std::min(qcap, atoi(v)));
+    return qcap;
+}
+
 int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta, float eps, int group_begin,
-             int group_count, bool count, cudaStream_t stream) {
+             int group_count, bool count, cudaStream_t stream, const WalkEpilogue& epi = WalkEpilogue{}) {
     nb_bh_state* st = ctx->bh;
     const float4* pos = reinterpret_cast<const float4*>(pos_);
     float4* acc = reinterpret_cast<float4*>(acc_);
     if (group_count <= 0) return NB_OK;
     if (n == 1) {
-        zero_acc_kernel<<<1, 32, 0, stream>>>(acc, 1);
+        if (epi.mode == 0) zero_acc_kernel<<<1, 32, 0, stream>>>(acc, 1);
+        else lone_body_kernel<<<1, 32, 0, stream>>>(pos, acc, epi);
         return NB_OK;
     }
     static const int use_dfs = [] { const char* v = getenv("NB_BH_WALK"); return (v && v[0] == 'd') ? 1 : 0; }();
+    if (use_dfs && epi.mode != 0) return nb_fail(ctx, NB_ERR_INVALID, "NB_BH_WALK=dfs has no fused kick/drift epilogue");
     if (count) cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
     if (use_dfs) {   // depth-first walk in the reference's own order (kept for comparison: NB_BH_WALK=dfs)
         const int blocks = (group_count + WALK_WARPS - 1) / WALK_WARPS;
@@ -1143,11 +1323,12 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
         int split = group_count >= busy ? 1 : (2 * group_count >= busy ? 2 : 4);
         if (forced_split == 1 || forced_split == 2 || forced_split == 4) split = forced_split;
         const int blocks = (group_count * split + WL_WARPS - 1) / WL_WARPS;
+        const int qcap = walk_qcap();
         const uint32_t* links = reinterpret_cast<const uint32_t*>(st->clink);
 #define NB_LAUNCH_WALK(COUNTING, SPLIT)                                                                               \
     walk_lists_kernel<COUNTING, SPLIT><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, \
                                                                             st->spos, st->root_rec, eps, group_begin,         \
-                                                                            group_count, acc, st->counters)
+                                                                            group_count, acc, st->counters, qcap, epi)
         if (count) {
             if (split == 1) NB_LAUNCH_WALK(true, 1); else if (split == 2) NB_LAUNCH_WALK(true, 2); else NB_LAUNCH_WALK(true, 4);
         } else {
@@ -1206,7 +1387,8 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     // launch-bound sizes: replay a captured graph of the same evaluation
     nb_bh_state* st = ctx->bh;
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
-    const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening, st->sort_full};
+    const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening, st->sort_full,
+                                      walk_qcap()};
     if (!st->graph_exec || !(st->graph_key == key)) {
         if (st->graph_exec) { cudaGraphExecDestroy(st->graph_exec); st->graph_exec = nullptr; }
         if (!st->capture_stream) NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->capture_stream, cudaStreamNonBlocking));
@@ -1225,6 +1407,65 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     st->last_n = n;
     st->bounds_valid = true;
     NB_CUDA(ctx, cudaGraphLaunch(st->graph_exec, (cudaStream_t)stream));
+    return NB_OK;
+}
+
+int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_bh_step* step, void* stream_) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (!step) return nb_fail(ctx, NB_ERR_INVALID, "step description is NULL");
+    int rc = check_args(ctx, pos, vel, n, step->theta);
+    if (rc) return rc;
+    if (!nb_softening_ok(step->softening)) return nb_fail(ctx, NB_ERR_INVALID, "softening must be >= 0");
+    const float eps = nb_effective_softening(step->softening);
+    auto drift_ok = [](int k) { return k >= NB_DRIFT_NONE && k <= NB_DRIFT_VDT_F64; };   // NB_DRIFT_VV_F64 needs the old acceleration
+    auto kick_ok = [](int k) { return k >= NB_KICK_NONE && k <= NB_KICK_DTA_F64; };      // NB_KICK_MEAN_F64 needs two
+    if (!drift_ok(step->pre_drift_kind) || !drift_ok(step->drift_kind) || !kick_ok(step->kick_kind) ||
+        !drift_ok(step->prev_drift_kind))
+        return nb_fail(ctx, NB_ERR_INVALID, "kick/drift kind not available in the fused step (Velocity Verlet needs nb_integrate_substep)");
+    if (n == 0) return NB_OK;
+    const int groups = (n + 31) / 32;
+    if (step->group_begin < 0 || step->group_count < 0 || step->group_begin + step->group_count > groups)
+        return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
+    if (step->flags & NB_BH_COUNT_WALK) return nb_fail(ctx, NB_ERR_INVALID, "the fused step has no instrumented walk");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t stream = (cudaStream_t)stream_;
+    rc = ensure_state(ctx, n);
+    if (rc) return rc;
+    nb_bh_state* st = ctx->bh;
+    PrepArgs prep{};
+    prep.pos_rw = reinterpret_cast<float4*>(pos);
+    prep.vel_rw = reinterpret_cast<float4*>(vel);
+    prep.pre = SubstepArgs{NB_KICK_NONE, step->pre_drift_kind, step->dt, 0.0, step->pre_drift_coef};
+    if (step->rows_in) {
+        // the rows are in the order of the LAST evaluation on this handle: its permutation is still in the sort buffers
+        if (!st->perm_valid || st->last_n != n)
+            return nb_fail(ctx, NB_ERR_INVALID, "rows_in needs a previous nb_bh_step_groups call with the same n on this handle");
+        prep.mode = 2;
+        prep.rows = reinterpret_cast<const float4*>(step->rows_in);
+        prep.perm = st->idx32[st->sfc_sel];
+        prep.post = SubstepArgs{NB_KICK_NONE, step->prev_drift_kind, step->dt, 0.0, step->prev_drift_coef};
+    } else {
+        prep.mode = step->pre_drift_kind != NB_DRIFT_NONE ? 1 : 0;
+    }
+    WalkEpilogue epi{};
+    epi.mode = step->rows_out ? 2 : 1;
+    epi.pos_rw = reinterpret_cast<float4*>(pos);
+    epi.vel_rw = reinterpret_cast<float4*>(vel);
+    epi.rows = reinterpret_cast<float4*>(step->rows_out);
+    epi.row_base = step->group_begin * 32;
+    epi.s = SubstepArgs{step->kick_kind, step->drift_kind, step->dt, step->kick_coef, step->drift_coef};
+    epi.stats = step->stats_out;
+    pick_sort_mode(st);
+    st->perm_valid = false;
+    // nothing to walk, kick or drift: only the first kernel runs (it brings pos / vel up to date from rows_in).  A rank
+    // that merely owns no groups still sorts: the next call needs this evaluation's permutation.
+    const bool only_prep = step->group_count == 0 && step->kick_kind == NB_KICK_NONE && step->drift_kind == NB_DRIFT_NONE;
+    rc = run_build(ctx, pos, n, step->flags, only_prep ? 1 : 4, step->theta, stream, prep);
+    if (rc) return rc;
+    if (only_prep) return NB_OK;
+    rc = run_walk(ctx, pos, step->acc_out, n, step->theta, eps, step->group_begin, step->group_count, false, stream, epi);
+    if (rc) return rc;
+    st->perm_valid = true;
     return NB_OK;
 }
 
@@ -1328,6 +1569,33 @@ int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* 
             mass[k] = cells[k].m; cx[k] = cells[k].cx; cy[k] = cells[k].cy;
         }
     }
+    return NB_OK;
+}
+
+int nb_bh_build_info(nb_context* ctx, int64_t info[4]) {
+    if (!ctx || !info) return NB_ERR_INVALID;
+    nb_bh_state* st = ctx->bh;
+    if (!st || st->last_n < 1) return nb_fail(ctx, NB_ERR_INVALID, "no tree has been built on this handle");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaDeviceSynchronize());
+    const int n = st->last_n;
+    int nodes = 0;
+    if (n >= 2) {
+        int32_t a = 0, b = 0;
+        NB_CUDA(ctx, cudaMemcpy(&a, st->flag_scan + (n - 2), 4, cudaMemcpyDeviceToHost));
+        NB_CUDA(ctx, cudaMemcpy(&b, st->flag_blk + ((n - 2) >> SCAN_SHIFT), 4, cudaMemcpyDeviceToHost));
+        nodes = a + b;
+    }
+    uint32_t words[2] = {0, 0};
+    NB_CUDA(ctx, cudaMemcpy(words, st->os_ticket + FIX_COUNT_WORD, sizeof(words), cudaMemcpyDeviceToHost));
+    std::vector<int8_t> lev(nodes > 0 ? nodes : 1, 0);
+    if (nodes > 0) NB_CUDA(ctx, cudaMemcpy(lev.data(), st->node_level, (size_t)nodes, cudaMemcpyDeviceToHost));
+    int deepest = 0;
+    for (int k = 0; k < nodes; k++) deepest = std::max(deepest, (int)lev[k]);
+    info[0] = nodes;
+    info[1] = words[0];
+    info[2] = (words[1] ? 1 : 0) | (st->sort_full ? 2 : 0);
+    info[3] = deepest;
     return NB_OK;
 }
 

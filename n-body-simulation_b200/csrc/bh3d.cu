@@ -75,7 +75,8 @@ constexpr int DIGITS3 = 8;
 
 // ---- bounds ---------------------------------------------------------------------------------------------
 __global__ void bounds3_kernel(const float4* __restrict__ pos, int n, float4* part, unsigned int* __restrict__ ticket,
-                               float4* __restrict__ bounds) {
+                               float4* __restrict__ bounds,
+                               unsigned long long* __restrict__ walk_status) {
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 p = pos[i];
@@ -122,6 +123,7 @@ __global__ void bounds3_kernel(const float4* __restrict__ pos, int n, float4* pa
         bounds[1] = make_float4(__fmaf_rn(fabsf(hi[0]), 0.001f, hi[0]), __fmaf_rn(fabsf(hi[1]), 0.001f, hi[1]),
                                 __fmaf_rn(fabsf(hi[2]), 0.001f, hi[2]), 0.f);
         *ticket = 0u;
+        *walk_status = 0ull;
     }
 }
 
@@ -352,6 +354,9 @@ __global__ void __launch_bounds__(256) emit3_kernel(TreeView3 t, const float4* _
 constexpr int W3_WARPS = 4;
 constexpr int W3_QCAP = 1024;
 constexpr int W3_LCAP = 64;
+// as WL_DFS_ROOM in bh.cu: past `qcap` entries a group finishes depth-first, which adds at most 7 entries per
+// remaining level (7 * 21 = 147) on top of the batch being pushed (<= 32)
+constexpr int W3_DFS_ROOM = 192;
 constexpr float FAR_AWAY3 = 3.0e18f;           // coordinate of a padding record: zero mass, contributes exactly 0
 
 __device__ __forceinline__ float rsqrt3_approx(float x) {
@@ -368,7 +373,7 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
                                                                 const float4* __restrict__ spos,
                                                                 const float4* __restrict__ root_rec, float eps,
                                                                 int group_begin, int group_count, float4* __restrict__ acc,
-                                                                unsigned long long* __restrict__ counters) {
+                                                                unsigned long long* __restrict__ counters, int qcap) {
     __shared__ uint32_t q_s[W3_WARPS][W3_QCAP];
     // pending accepted records, two per slot (FP32x2 evaluation): (cx0, cx1, cy0, cy1) and (cz0, cz1, m0, m1)
     __shared__ float4 lxy_s[W3_WARPS][W3_LCAP / 2];
@@ -412,7 +417,7 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
     int qtop = 0, lcount = 0;
     unsigned long long c_open = 0, c_exam = 0, c_inter = 0;
     int c_depth = 0;
-    bool overflow = false;
+    bool depth_first = false;
 
     auto add = [&](float cx, float cy, float cz, float m) {        // src/DirectComputeKernels.cu:61-67
         const float dx = cx - x, dy = cy - y, dz = cz - z;
@@ -513,11 +518,53 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         if (accp) append(lcount + __popc(accm & below), rec);
         lcount += __popc(accm);
         const int nrej = __popc(rejm);
-        if (qtop + nrej > W3_QCAP) { overflow = true; break; }
+        if (qtop + nrej > qcap) depth_first = true;   // room for this batch is reserved (W3_DFS_ROOM)
         if (rej) q[qtop + __popc(rejm & below)] = link;
         qtop += nrej;
         __syncwarp();
         if (COUNT) c_depth = max(c_depth, qtop);
+        if (depth_first) {   // the rest of this group's walk one node at a time, every lane voting on the same child
+            while (qtop > 0) {
+                const uint32_t ent = q[qtop - 1];
+                __syncwarp();
+                qtop--;
+                if (COUNT) c_open++;
+                const size_t id = ent & 0x7FFFFFFFu;
+                if (ent & LINK_BUCKET) {
+                    const float4 h = crec[8 * id];
+                    const int first = __float_as_int(h.x), cnt = __float_as_int(h.y);
+                    for (int t = 0; t < cnt; t++) {
+                        const float4 p = spos[first + t];
+                        add(p.x, p.y, p.z, p.w);
+                    }
+                    if (COUNT) { c_exam += cnt; c_inter += cnt; }
+                    continue;
+                }
+                for (int c = 0; c < 8; c++) {
+                    const uint32_t lk = clink[8 * id + c];
+                    if (lk == LINK_EMPTY) continue;
+                    const float4 r4 = crec[8 * id + c];
+                    const float ct = cthr[8 * id + c];
+                    const float dx = r4.x - x, dy = r4.y - y, dz = r4.z - z;
+                    const float r = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmaf_rn(dx, dx, eps)));
+                    if (COUNT) c_exam++;
+                    if (__all_sync(FULLM, ct <= r)) {
+                        const float inv = rsqrt3_approx(r);
+                        const float k = inv * inv * inv * r4.w;
+                        ax = __fmaf_rn(k, dx, ax);
+                        ay = __fmaf_rn(k, dy, ay);
+                        az = __fmaf_rn(k, dz, az);
+                        if (COUNT) c_inter++;
+                    } else {
+                        if (lane == 0) q[qtop] = lk;
+                        qtop++;
+                    }
+                }
+                __syncwarp();
+                if (COUNT) c_depth = max(c_depth, qtop);
+            }
+            break;
+        }
         if (qtop == 0) break;
         // pop up to four nodes: lane l takes child (l & 7) of the (l >> 3)-th node from the top
         const int k = min(4, qtop);
@@ -558,7 +605,7 @@ __global__ void __launch_bounds__(W3_WARPS * 32, 6) walk3_kernel(const float4* _
         up2(AZ2, a0, a1); az += a0 + a1;
     }
     if (valid) acc[body] = make_float4(ax, ay, az, 0.f);
-    if (overflow && lane == 0) atomicOr(&counters[4], 1ull);
+    if (depth_first && lane == 0) atomicOr(&counters[4], 1ull);   // informative: a group left the batched schedule
     if (COUNT && lane == 0) {
         atomicAdd(&counters[0], c_open);
         atomicAdd(&counters[1], c_exam);
@@ -576,6 +623,7 @@ __global__ void zero_acc3_kernel(float4* acc, int n) {
 template <typename T>
 int alloc3(nb_context* ctx, T** p, size_t count) {
     NB_CUDA(ctx, cudaMalloc((void**)p, count * sizeof(T)));
+    ctx->bh3_bytes += count * sizeof(T);
     return NB_OK;
 }
 
@@ -595,6 +643,7 @@ int ensure_state3(nb_context* ctx, int n) {
         free_state3(ctx->bh3);
         delete ctx->bh3;
         ctx->bh3 = nullptr;
+        ctx->bh3_bytes = 0;
     }
     nb_bh3_state* st = new nb_bh3_state();
     ctx->bh3 = st;
@@ -645,7 +694,7 @@ int run_build3(nb_context* ctx, const float* pos_, int n, int upto, float theta,
     const float4* pos = reinterpret_cast<const float4*>(pos_);
     st->last_n = n;
     const int bblocks = std::min(1024, std::max(1, (n + 1023) / 1024));
-    bounds3_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds);
+    bounds3_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, st->counters + 4);
     if (upto >= 2) {
         const int tiles = (n + SORT_TILE - 1) / SORT_TILE;
         st->os_stride = (size_t)tiles * 256;
@@ -709,15 +758,17 @@ int nb_bh3d_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, f
         return NB_OK;
     }
     const int blocks = (group_count + W3_WARPS - 1) / W3_WARPS;
+    int qcap = W3_QCAP - W3_DFS_ROOM;
+    if (const char* v = getenv("NB_BH_WALK_QCAP")) qcap = std::max(0, std::min(qcap, atoi(v)));   // tests: force the depth-first path
     if (flags & NB_BH_COUNT_WALK) {
         cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
         walk3_kernel<true><<<blocks, W3_WARPS * 32, 0, stream>>>((const float4*)pos, st->idx[st->sel], n, st->crec, st->cthr, st->clink,
                                                                 st->spos, st->root_rec, softening, group_begin, group_count,
-                                                                (float4*)acc, st->counters);
+                                                                (float4*)acc, st->counters, qcap);
     } else {
         walk3_kernel<false><<<blocks, W3_WARPS * 32, 0, stream>>>((const float4*)pos, st->idx[st->sel], n, st->crec, st->cthr, st->clink,
                                                                  st->spos, st->root_rec, softening, group_begin, group_count,
-                                                                 (float4*)acc, st->counters);
+                                                                 (float4*)acc, st->counters, qcap);
     }
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;

@@ -28,9 +28,13 @@ struct nb_context {
     void* dev_acc = nullptr;
     size_t dev_pos_bytes = 0, dev_acc_bytes = 0;
     int last_jsplit = 0, last_blocks = 0, last_launches = 0;
+    // resident CTAs per SM of each direct-kernel variant ON THIS DEVICE, 0 = the shared-memory opt-in has not been
+    // made here yet (cudaFuncSetAttribute is per device: a process-wide cache would skip it on a second GPU)
+    int direct_occ[2][2][2] = {};
 
     nb_bh_state* bh = nullptr;
     nb_bh3_state* bh3 = nullptr;
+    size_t bh_bytes = 0, bh3_bytes = 0;   // device memory held by the two Barnes-Hut states
     cudaStream_t host_stream = nullptr;  // used by the *_host entry points
 };
 

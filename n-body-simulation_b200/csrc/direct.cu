@@ -70,7 +70,8 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
               const unsigned char* __restrict__ tile_uniform,   // HOIST: 1 where all 1024 masses of a tile equal m_ref
               const float* __restrict__ mref) {                 // HOIST: [0] = m_ref, [1] = 1/m_ref
     float m_ref = 1.f, inv_mref = 1.f;
-    if (HOIST) { m_ref = mref[0]; inv_mref = mref[1]; }
+    bool hoist_on = false;
+    if (HOIST) { m_ref = mref[0]; inv_mref = mref[1]; hoist_on = mref[2] != 0.f; }
     extern __shared__ __align__(128) unsigned char smem[];
     const float4* tiles = reinterpret_cast<const float4*>(smem);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * TILE * REC_BYTES);
@@ -125,7 +126,7 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
         mbar_wait(&full[s], (it / STAGES) & 1);
         const float4* tp = tiles + s * TILE;
         const int cnt = tile_count(tile0 + it);
-        if (HOIST && cnt == TILE && tile_uniform[tile0 + it]) {
+        if (HOIST && hoist_on && cnt == TILE && tile_uniform[tile0 + it]) {
 #pragma unroll 4
             for (int j = 0; j < TILE; j++) interact<DIM, PAIRS, true>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, 1.f, false);
         } else if (cnt == TILE) {
@@ -184,22 +185,59 @@ __global__ void zero_acc_kernel(float4* acc, int n) {
     if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-// Per source tile: are all masses equal to the reference mass (the mass of body n/2)?  m_ref <= 0 or non-finite
-// disables hoisting (no tile is marked).
+// Per source tile: are all masses equal to the reference mass (the mass of body n/2)?  The last block to finish then
+// decides whether hoisting is safe at all: m_ref must be a normal positive number with a finite reciprocal, and the
+// largest |m_j| / m_ref (what a mixed tile carries instead of m_j) must stay finite in FP32.  Otherwise mref[2] = 0 and
+// the force kernel takes the exact 12-operation path for every tile with the raw masses.
 __global__ void __launch_bounds__(256) classify_tiles_kernel(const float4* __restrict__ pos, int n,
                                                             unsigned char* __restrict__ tile_uniform,
-                                                            float* __restrict__ mref) {
+                                                            float* __restrict__ mref,      // [0] m_ref, [1] 1/m_ref, [2] hoisting on
+                                                            unsigned int* __restrict__ ticket,
+                                                            float* __restrict__ tile_max) {
+    __shared__ float red[8];
+    __shared__ bool last;
     const float m = pos[n / 2].w;
-    const bool usable = m > 0.f && m < 3.0e38f;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        mref[0] = usable ? m : 1.f;
-        mref[1] = usable ? 1.f / m : 1.f;
-    }
+    const bool usable = m >= 1.0e-30f && m <= 1.0e30f;
     const int base = blockIdx.x * TILE;
     int same = 1;
-    for (int j = threadIdx.x; j < TILE; j += blockDim.x) same &= (base + j < n && pos[base + j].w == m) ? 1 : 0;
+    float mx = 0.f;
+    for (int j = threadIdx.x; j < TILE; j += blockDim.x) {
+        const bool in = base + j < n;
+        const float w = in ? pos[base + j].w : 0.f;
+        same &= (in && w == m) ? 1 : 0;
+        mx = fmaxf(mx, fabsf(w));
+    }
     same = __syncthreads_and(same);
-    if (threadIdx.x == 0) tile_uniform[blockIdx.x] = (usable && same) ? 1 : 0;
+    auto block_max = [&](float v) {
+        for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+        __syncthreads();
+        v = red[0];
+        for (int w = 1; w < 8; w++) v = fmaxf(v, red[w]);
+        __syncthreads();
+        return v;
+    };
+    mx = block_max(mx);
+    if (threadIdx.x == 0) {
+        tile_uniform[blockIdx.x] = (usable && same) ? 1 : 0;
+        tile_max[blockIdx.x] = mx;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    float g = 0.f;
+    for (int b = threadIdx.x; b < gridDim.x; b += blockDim.x) g = fmaxf(g, __ldcg(&tile_max[b]));
+    g = block_max(g);
+    if (threadIdx.x == 0) {
+        const float inv = usable ? 1.f / m : 1.f;
+        const bool ok = usable && g * inv <= 1.0e30f;   // false for inf / NaN as well
+        mref[0] = ok ? m : 1.f;
+        mref[1] = ok ? inv : 1.f;
+        mref[2] = ok ? 1.f : 0.f;
+        *ticket = 0u;
+    }
 }
 
 using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int, const unsigned char*, const float*);
@@ -207,14 +245,13 @@ using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int, co
 struct Variant {
     kernel_fn fn;
     int pairs;
-    int occupancy;  // resident CTAs per SM, filled lazily
 };
 
-Variant g_variants[2][2][2] = {   // [hoist][dim - 2][pairs == 4]
-    {{{direct_kernel<2, 2, 3, false>, 2, 0}, {direct_kernel<2, 4, 2, false>, 4, 0}},
-     {{direct_kernel<3, 2, 3, false>, 2, 0}, {direct_kernel<3, 4, 2, false>, 4, 0}}},
-    {{{direct_kernel<2, 2, 3, true>, 2, 0}, {direct_kernel<2, 4, 2, true>, 4, 0}},
-     {{direct_kernel<3, 2, 3, true>, 2, 0}, {direct_kernel<3, 4, 2, true>, 4, 0}}},
+const Variant g_variants[2][2][2] = {   // [hoist][dim - 2][pairs == 4]; per-device state lives in nb_context::direct_occ
+    {{{direct_kernel<2, 2, 3, false>, 2}, {direct_kernel<2, 4, 2, false>, 4}},
+     {{direct_kernel<3, 2, 3, false>, 2}, {direct_kernel<3, 4, 2, false>, 4}}},
+    {{{direct_kernel<2, 2, 3, true>, 2}, {direct_kernel<2, 4, 2, true>, 4}},
+     {{direct_kernel<3, 2, 3, true>, 2}, {direct_kernel<3, 4, 2, true>, 4}}},
 };
 
 int env_int(const char* name, int dflt) {
@@ -245,17 +282,18 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     if (pairs != 2 && pairs != 4) pairs = (target_count >= ctx->sm_count * 2 * NT * 8) ? 4 : 2;
     // Hoisting the common mass out of the sum changes the rounding (not the order) of the sum: exact mode keeps
     // the reference arithmetic; NB_DIRECT_NO_HOIST switches it off for tuning.
-    const bool hoist = !(flags & NB_DIRECT_ORDERED) && env_int("NB_DIRECT_NO_HOIST", 0) == 0;
-    Variant& v = g_variants[hoist ? 1 : 0][dim - 2][pairs == 4 ? 1 : 0];
-    if (v.occupancy == 0) {
+    const bool hoist = !(flags & (NB_DIRECT_ORDERED | NB_DIRECT_NO_HOIST)) && env_int("NB_DIRECT_NO_HOIST", 0) == 0;
+    const Variant& v = g_variants[hoist ? 1 : 0][dim - 2][pairs == 4 ? 1 : 0];
+    int& occupancy = ctx->direct_occ[hoist ? 1 : 0][dim - 2][pairs == 4 ? 1 : 0];
+    if (occupancy == 0) {   // first use of this variant on the handle's device (the current device, set above)
         NB_CUDA(ctx, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         int occ = 0;
         NB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, NT, SMEM_BYTES));
-        v.occupancy = occ > 0 ? occ : 1;
+        occupancy = occ > 0 ? occ : 1;
     }
     const int per_block = NT * 2 * v.pairs;
     const int tblocks = (target_count + per_block - 1) / per_block;
-    const int slots = ctx->sm_count * v.occupancy;
+    const int slots = ctx->sm_count * occupancy;
 
     // split the source range so that the grid is close to a whole number of waves
     int jsplit = 1;
@@ -269,6 +307,7 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
             if (max_js < 1) max_js = 1;
             double best = -1.0;
             for (int js = 1; js <= max_js; js++) {
+                if (js > 1 && (size_t)js * target_count * sizeof(float4) > ((size_t)1 << 30)) break;   // partial sums: <= 1 GiB
                 long long blocks = (long long)tblocks * js;
                 long long waves = (blocks + slots - 1) / slots;
                 double eff = (double)blocks / (double)(waves * slots);
@@ -293,11 +332,17 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     unsigned char* flags_d = nullptr;
     float* mref_d = nullptr;
     if (hoist) {
-        rc = nb_reserve(ctx, &ctx->tile_flags, &ctx->tile_flags_bytes, (size_t)ntiles + 64);
+        // layout: 64-byte header (m_ref, 1/m_ref, hoisting on, ticket) | one byte per tile | one float per tile
+        const size_t flag_bytes = ((size_t)ntiles + 63) & ~(size_t)63;
+        const size_t had = ctx->tile_flags_bytes;
+        rc = nb_reserve(ctx, &ctx->tile_flags, &ctx->tile_flags_bytes, 64 + flag_bytes + (size_t)ntiles * sizeof(float));
         if (rc) return rc;
+        if (ctx->tile_flags_bytes != had) NB_CUDA(ctx, cudaMemset(ctx->tile_flags, 0, 64));   // the ticket starts at 0
         mref_d = reinterpret_cast<float*>(ctx->tile_flags);
         flags_d = reinterpret_cast<unsigned char*>(ctx->tile_flags) + 64;
-        classify_tiles_kernel<<<ntiles, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, flags_d, mref_d);
+        classify_tiles_kernel<<<ntiles, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, flags_d, mref_d,
+                                                          reinterpret_cast<unsigned int*>(ctx->tile_flags) + 4,
+                                                          reinterpret_cast<float*>(flags_d + flag_bytes));
         launches++;
     }
     dim3 grid(tblocks, jsplit);

@@ -93,6 +93,7 @@ int nb_ic_uniform_ellipsoid(nb_context* ctx, float* pos, float* vel, int offset,
     if (!ctx) return NB_ERR_INVALID;
     if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
     ellipsoid_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, offset, count, seed, cx, cy, rx,
                                                                            ry, z_half_height, mass, central_mass, vx, vy);
     NB_CUDA(ctx, cudaGetLastError());
@@ -106,6 +107,7 @@ int nb_ic_uniform_box(nb_context* ctx, float* pos, float* vel, int offset, int c
     if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
     if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
     box_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, offset, count, seed, cx, cy, sx, sy,
                                                                      dim, mass_lo, mass_hi, speed_lo, speed_hi, vx, vy);
     NB_CUDA(ctx, cudaGetLastError());
@@ -118,6 +120,7 @@ int nb_ic_disk_velocities(nb_context* ctx, const float* pos, const float* acc, f
     if (begin < 0 || count < 0 || (count > 0 && (!pos || !acc || !vel))) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
     if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
     disk_velocity_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const float4*)pos, (const float4*)acc, (float4*)vel,
                                                                                begin, count, cx, cy, dim, bulk_vx, bulk_vy);
     NB_CUDA(ctx, cudaGetLastError());

@@ -53,6 +53,7 @@ int nb_verlet_dkd_drift(nb_context* ctx, float* pos, const float* vel, int begin
     if (!ctx) return NB_ERR_INVALID;
     if (begin < 0 || count < 0) return nb_fail(ctx, NB_ERR_INVALID, "bad slice");
     if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
     verlet_dkd_drift_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (const float4*)vel,
                                                                                   begin, count, dt);
     NB_CUDA(ctx, cudaGetLastError());
@@ -64,6 +65,7 @@ int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const floa
     if (!ctx) return NB_ERR_INVALID;
     if (begin < 0 || count < 0) return nb_fail(ctx, NB_ERR_INVALID, "bad slice");
     if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
     verlet_dkd_kick_drift_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
         (float4*)pos, (float4*)vel, (const float4*)acc, begin, count, dt);
     NB_CUDA(ctx, cudaGetLastError());
@@ -77,35 +79,9 @@ int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const floa
 // The kinds reproduce the reference's mixed FP32/FP64 expression types: a `double`
 // literal or coefficient promotes the whole product to FP64 and the result is rounded once on the `+=`.
 // ------------------------------------------------------------------------------------------------------
+#include "integrate.cuh"
+
 namespace {
-
-struct SubstepArgs {
-    int kick, drift;
-    float dt;
-    double ck, cd;
-};
-
-__device__ __forceinline__ float kick1(const SubstepArgs& s, float v, float a, float ap) {
-    switch (s.kick) {
-        case NB_KICK_F32:       return fmaf(s.dt, a, v);                                          // vel += dt * acc
-        case NB_KICK_HALF_F64:  return (float)__fma_rn((double)s.dt * 0.5, (double)a, (double)v);  // vel += dt * 0.5 * acc
-        case NB_KICK_COEF_F64:  return (float)__fma_rn(s.ck, (double)a, (double)v);                // vel += (c*dt) * acc      (PEFRL)
-        case NB_KICK_DTA_F64:   return (float)__fma_rn((double)(s.dt * a), s.ck, (double)v);       // vel += dt * acc * c      (Forest-Ruth)
-        case NB_KICK_MEAN_F64:  return (float)__fma_rn(0.5 * (double)s.dt, (double)(a + ap), (double)v);  // vel += 0.5*dt*(acc+prev)
-        default:                return v;
-    }
-}
-__device__ __forceinline__ float drift1g(const SubstepArgs& s, float p, float v, float a) {
-    switch (s.drift) {
-        case NB_DRIFT_F32:      return fmaf(v, s.dt, p);                                           // pos += vel * dt
-        case NB_DRIFT_HALF_F64: return (float)__fma_rn((double)v, (double)s.dt * 0.5, (double)p);   // pos += vel * (dt * 0.5)
-        case NB_DRIFT_COEF_F64: return (float)__fma_rn(s.cd, (double)v, (double)p);                 // pos += (c*dt) * vel      (PEFRL)
-        case NB_DRIFT_VDT_F64:  return (float)__fma_rn(__dmul_rn((double)(v * s.dt), s.cd), 0.5, (double)p);   // pos += vel*dt*c*0.5 (Forest-Ruth)
-        case NB_DRIFT_VV_F64:   // pos += vel*dt + acc*0.5*dt*dt   (Velocity Verlet)
-            return (float)((double)p + ((double)(v * s.dt) + __dmul_rn(__dmul_rn((double)a * 0.5, (double)s.dt), (double)s.dt)));
-        default:                return p;
-    }
-}
 
 __global__ void substep_kernel(float4* __restrict__ pos, float4* __restrict__ vel, const float4* __restrict__ acc,
                                const float4* __restrict__ acc_prev, int begin, int count, SubstepArgs s) {
@@ -141,6 +117,7 @@ extern "C" int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, con
         return nb_fail(ctx, NB_ERR_INVALID, "unknown kick/drift kind");
     if (kick_kind == NB_KICK_MEAN_F64 && !acc_prev) return nb_fail(ctx, NB_ERR_INVALID, "NB_KICK_MEAN_F64 needs acc_prev");
     if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
     SubstepArgs s{kick_kind, drift_kind, dt, kick_coef, drift_coef};
     substep_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, (const float4*)acc,
                                                                          (const float4*)acc_prev, begin, count, s);

@@ -104,3 +104,27 @@ def clustered(n, seed=5, clusters=8, radius=30000.0, sigma=40.0, mass=70000.0):
     pos[:, 1] = (cy[which] + rr * np.sin(2 * np.pi * u2)).astype(np.float32)
     pos[:, 3] = np.float32(mass)
     return pos
+
+
+def cold_collapse_late(n, seed=2, radius=30000.0, mass=70000.0, clumps=12):
+    """A late cold-collapse state (config 4 of BASELINE.json: deep clustered tree, load imbalance): 70 % of the bodies
+    sit in `clumps` Gaussian knots whose widths span three decades (5 ... 2000 length units, so the tree is 10 levels
+    deeper inside the tightest knot than in the field), populated unequally (weights 1 ... clumps), over a diffuse disc
+    holding the remaining 30 %.  Counter-based, same bodies on every host."""
+    cx = (uniform01(seed, 20, clumps) * 2 - 1) * 0.6 * radius
+    cy = (uniform01(seed, 21, clumps) * 2 - 1) * 0.6 * radius
+    sigma = 5.0 * (400.0 ** (np.arange(clumps) / max(clumps - 1, 1)))
+    w = np.arange(1, clumps + 1, dtype=np.float64)
+    cdf = np.cumsum(w) / w.sum()
+    u = uniform01(seed, 22, n)
+    in_clump = u < 0.7
+    which = np.minimum(np.searchsorted(cdf, u / 0.7), clumps - 1)
+    u1 = np.maximum(uniform01(seed, 23, n), 1e-12)
+    u2 = uniform01(seed, 24, n)
+    rr = sigma[which] * np.sqrt(-2.0 * np.log(u1))
+    disc = uniform_disk(n, seed=seed, radius=radius, mass=mass)
+    pos = disc.copy()
+    pos[:, 0] = np.where(in_clump, (cx[which] + rr * np.cos(2 * np.pi * u2)), disc[:, 0]).astype(np.float32)
+    pos[:, 1] = np.where(in_clump, (cy[which] + rr * np.sin(2 * np.pi * u2)), disc[:, 1]).astype(np.float32)
+    pos[:, 3] = np.float32(mass)
+    return pos

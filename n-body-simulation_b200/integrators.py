@@ -147,3 +147,105 @@ class ShardedSystem:
                 if self.world > 1:
                     self.dist.all_reduce(self._acc_full)
                 self.acc.copy_(self._acc_full[self.begin:self.end])
+
+
+# Every stepper except Velocity Verlet as  pre-force drift + [force; kick; drift]*  (kind, coefficient) pairs -- the
+# kernel sequences of src/IntegrationMethods.cu:26-35, 58-67, 96-105, 245-270, 343-374.  `d` is float(np.float32(dt)).
+def stepper_program(name, dt):
+    d = float(np.float32(dt))
+    if name == "Euler_Symplectic_KD":
+        return (DRIFT_NONE, 0.0), [((KICK_F32, 0.0), (DRIFT_F32, 0.0))]
+    if name == "Euler_Symplectic_DK":
+        return (DRIFT_F32, 0.0), [((KICK_F32, 0.0), (DRIFT_NONE, 0.0))]
+    if name == "Verlet_DKD":
+        return (DRIFT_HALF_F64, 0.0), [((KICK_F32, 0.0), (DRIFT_HALF_F64, 0.0))]
+    if name == "ForestRuth":
+        O = IntegrationMethods.ForestRuth.O
+        return (DRIFT_VDT_F64, O), [((KICK_DTA_F64, O), (DRIFT_VDT_F64, 1 - O)),
+                                    ((KICK_DTA_F64, 1 - 2 * O), (DRIFT_VDT_F64, 1 - O)),
+                                    ((KICK_DTA_F64, O), (DRIFT_VDT_F64, O))]
+    if name == "PEFRL":
+        P = IntegrationMethods.PEFRL
+        Et, Xt, Lt = P.E * d, P.X * d, P.L * d
+        mL = (1 + 2 * 0.2123418310626054) / 2 * d
+        kt = (1 - 2 * (0.1786178958448091 - 0.06626458266981849)) * d
+        return (DRIFT_COEF_F64, Et), [((KICK_COEF_F64, mL), (DRIFT_COEF_F64, Xt)), ((KICK_COEF_F64, Lt), (DRIFT_COEF_F64, kt)),
+                                      ((KICK_COEF_F64, Lt), (DRIFT_COEF_F64, Xt)), ((KICK_COEF_F64, mL), (DRIFT_COEF_F64, Et))]
+    raise ValueError(f"{name} has no fused form (Velocity_Verlet and Verlet_KDK need the previous acceleration)")
+
+
+class FusedBarnesHut:
+    """Barnes-Hut time stepping with the kick and drift fused into the walk (nb_bh_step_groups), on one GPU or sharded.
+
+    Sharded (world > 1): positions AND velocities are replicated on every rank; a rank walks its share of the 32-target
+    groups of the sorted order, its epilogue produces (x', y', vx', vy') rows in sorted order, ONE all-gather per force
+    evaluation (16 bytes per body) replicates them, and the next evaluation's first kernel scatters them back to body
+    order.  That replaces the all-gather of positions plus the N x 16-byte exchange of accelerations of ShardedSystem.
+    `pos` / `vel` are current after materialize() (called by step() unless lazy=True)."""
+
+    def __init__(self, engine, pos, vel, integrator="Verlet_DKD", theta=0.5, softening=1.01, world=1, rank=0, dist=None,
+                 flags=0, stats=False):
+        import torch
+        from . import shard
+        self.engine, self.pos, self.vel = engine, pos, vel
+        self.n = pos.shape[0]
+        self.integrator, self.theta, self.eps, self.flags = integrator, theta, softening, flags
+        self.world, self.rank, self.dist = world, rank, dist
+        self.groups = (self.n + 31) // 32
+        self.g0, self.g1 = shard.group_bounds(self.n, world, rank)
+        self._bounds = [shard.group_bounds(self.n, world, r) for r in range(world)]
+        self.even = self.groups % world == 0
+        self.rows_all = self.rows_out = None
+        if world > 1:
+            self.rows_all = torch.empty(32 * self.groups, 4, device=pos.device)
+            self.rows_out = self.rows_all[32 * self.g0:32 * self.g1] if self.even else \
+                torch.empty(32 * (self.g1 - self.g0), 4, device=pos.device)
+        self.stats_buf = torch.zeros(2 * self.groups, dtype=torch.float64, device=pos.device) if stats else None
+        self.pending = None          # (drift kind, coefficient) of the evaluation whose rows are waiting in rows_all
+        self.force_evaluations = 0
+
+    def _gather_rows(self):
+        if self.even:                # in place: every rank's rows already sit at their offset of rows_all
+            self.dist.all_gather_into_tensor(self.rows_all, self.rows_out)
+        else:                        # ragged group counts: one broadcast per owner
+            self.rows_all[32 * self.g0:32 * self.g1].copy_(self.rows_out)
+            for r, (a, b) in enumerate(self._bounds):
+                self.dist.broadcast(self.rows_all[32 * a:32 * b], src=r)
+
+    def _group(self, dt, pre, kick, drift, stats):
+        e = self.engine
+        sharded = self.world > 1
+        rows_in, prev = (self.rows_all, self.pending) if self.pending is not None else (None, (0, 0.0))
+        e.bh_step_groups(self.pos, self.vel, self.theta, self.eps, dt, self.g0, self.g1 - self.g0, pre_drift=pre, kick=kick,
+                         drift=drift, rows_in=rows_in, prev_drift=prev, rows_out=self.rows_out if sharded else None,
+                         stats_out=self.stats_buf if stats else None, flags=self.flags)
+        self.force_evaluations += 1
+        if sharded:
+            self._gather_rows()
+            self.pending = drift
+
+    def materialize(self):
+        """Brings pos / vel (body order) up to date on this rank; a no-op on one GPU."""
+        if self.pending is not None:
+            self.engine.bh_step_groups(self.pos, self.vel, self.theta, self.eps, 0.0, 0, 0, rows_in=self.rows_all,
+                                       prev_drift=self.pending, flags=self.flags)
+            self.pending = None
+
+    def step(self, dt, lazy=False, stats=False):
+        pre, groups = stepper_program(self.integrator, dt)
+        for k, (kick, drift) in enumerate(groups):
+            self._group(dt, pre if k == 0 else (DRIFT_NONE, 0.0), kick, drift, stats and k == len(groups) - 1)
+        if not lazy:
+            self.materialize()
+        if stats:
+            return self.kinetic_stats()
+
+    def kinetic_stats(self):
+        """(sum m|v|, kinetic energy) of the whole system from the last step(stats=True): per-group partial sums of the
+        walk epilogue, added in group order; sharded runs all-reduce the two doubles."""
+        import torch
+        part = self.stats_buf.view(-1, 2)[self.g0:self.g1].sum(dim=0)
+        if self.world > 1:
+            self.dist.all_reduce(part)
+        m, k = part.tolist()
+        return m, k

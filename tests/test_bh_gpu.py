@@ -315,3 +315,79 @@ def test_dense_system_same_result_on_every_sort_path(pkg):
                 assert torch.equal(acc, first), rep
                 assert all(np.array_equal(tree[k], first_tree[k]) for k in ("prefix", "level", "count"))
         eng.close()
+
+
+@pytest.mark.parametrize("case", ["disk_8192", "clustered_8192", "duplicates_3000", "dense_knot_6000"])
+def test_full_queue_finishes_depth_first(engine, pkg, oracle, case, monkeypatch):
+    """A group whose node queue fills up finishes its walk in depth-first order instead of dropping nodes (the
+    reference's 64-entry stack overflows silently, src/BarnesHutKernels.cu:388).  NB_BH_WALK_QCAP lowers the threshold
+    so that nearly every group takes that path: same interaction count, same accelerations up to the order of the
+    FP32 sum, and the status bit says that it happened."""
+    import torch
+    pos = _cases(pkg)[case]
+    n = pos.shape[0]
+    dpos = _dev(pos)
+    want = torch.zeros(n, 4, device="cuda")
+    engine.bh_accel(dpos, want, 0.5, EPS, pkg.NB_BH_COUNT_WALK)
+    k0 = engine.bh_last_counters()
+    assert k0["status"] == 0
+    for qcap in (0, 8, 40):
+        monkeypatch.setenv("NB_BH_WALK_QCAP", str(qcap))
+        got = torch.full((n, 4), 3.0, device="cuda")
+        engine.bh_accel(dpos, got, 0.5, EPS, pkg.NB_BH_COUNT_WALK)
+        k1 = engine.bh_last_counters()
+        assert k1["status"] == 1 and k1["interactions"] == k0["interactions"], (qcap, k0, k1)
+        e = _rel(got.cpu().numpy(), want.cpu().numpy().astype(np.float64))
+        assert e.max() < 1e-4 and np.median(e) < 2e-6, (qcap, np.median(e), e.max())
+        plain = torch.full((n, 4), 3.0, device="cuda")          # the uninstrumented kernel (graph replay at this size)
+        engine.bh_accel(dpos, plain, 0.5, EPS)
+        torch.cuda.synchronize()
+        assert torch.equal(plain, got)
+    monkeypatch.delenv("NB_BH_WALK_QCAP")
+    again = torch.zeros(n, 4, device="cuda")
+    engine.bh_accel(dpos, again, 0.5, EPS)
+    torch.cuda.synchronize()
+    assert torch.equal(again, want) and engine.bh_last_counters()["status"] == 0
+
+
+def test_cold_collapse_one_million(pkg, oracle):
+    """BASELINE.json config 4 as specified: a genuinely clustered 1,048,576-body state (ics.cold_collapse_late: knots
+    three decades apart in width over a diffuse disc), theta = 0.5.  Checked: permutation validity, sortedness and
+    stability of the SFC order, the tree is 10+ levels deeper than the uniform disc's, no group left the batched walk
+    (queue depth stays under the threshold), which sort path ran, and 512 sampled bodies against the FP64 direct sum
+    within the theta-error of the method."""
+    import torch
+    n = 1 << 20
+    pos = pkg.ics.cold_collapse_late(n, seed=2)
+    eng = pkg.Engine(0, n)
+    dpos = _dev(pos)
+    st = eng.bh_stages(dpos)
+    si = st["sorted_idx"]
+    assert np.array_equal(np.sort(si), np.arange(n, dtype=np.int32))
+    sk = st["keys"][si]
+    assert np.all(sk[1:] >= sk[:-1])
+    ties = sk[1:] == sk[:-1]
+    assert np.all(si[1:][ties] > si[:-1][ties])
+    acc = torch.zeros(n, 4, device="cuda")
+    eng.bh_accel(dpos, acc, 0.5, EPS, pkg.NB_BH_COUNT_WALK)
+    torch.cuda.synchronize()
+    k = eng.bh_last_counters()
+    info = eng.bh_build_info()
+    assert k["status"] == 0 and k["max_stack"] <= 896, k
+    assert 0 < info["nodes"] < n and 20 <= info["deepest_level"] <= 32, info
+    sample = np.arange(0, n, n // 512)[:512]
+    got = acc.cpu().numpy()[sample]
+    ref = np.concatenate([oracle.direct_f64(pos, 2, EPS, t0=int(t), nt=1) for t in sample])
+    e = _rel(got, ref)
+    assert np.median(e) < 2e-3 and e.max() < 0.05, (np.median(e), e.max())
+    again = torch.zeros(n, 4, device="cuda")       # second evaluation: whichever sort path the host now asks for
+    eng.bh_accel(dpos, again, 0.5, EPS)
+    torch.cuda.synchronize()
+    assert torch.equal(again, acc)
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        import json
+        with open(os.path.join(out, "cold_collapse_1m.json"), "w") as f:
+            json.dump({"counters": k, "build": info, "theta_error_vs_fp64": {"median": float(np.median(e)),
+                       "p99": float(np.quantile(e, 0.99)), "max": float(e.max())}}, f, indent=1)
+    eng.close()

@@ -225,3 +225,110 @@ def test_call_sequence_keeps_no_stale_state(pkg):
         fresh.close()
         assert torch.equal(got, want), (it, n, dim, b, cnt, flags)
     eng.close()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_direct_extreme_masses_keep_the_general_path(engine, pkg, dim):
+    """The common-mass hoisting divides by the reference mass (body n/2) and carries m_j / m_ref in mixed tiles: a
+    subnormal or tiny reference mass, or a mass ratio beyond FP32, must switch the hoisting off instead of producing
+    inf / NaN.  Whatever the ordered (exact 12-operation) mode gives, the default mode must give too."""
+    n = 5000
+    base = pkg.ics.uniform_disk(n, seed=91, z_half_height=3000.0 if dim == 3 else 0.0)
+    cases = {
+        "subnormal_reference": np.where(np.arange(n) == n // 2, 1e-41, 7e4),
+        "tiny_reference_huge_other": np.where(np.arange(n) == n // 2, 1e-25, np.where(np.arange(n) == 7, 1e20, 3.0)),
+        "all_tiny": np.full(n, 1e-36),
+        "huge_uniform": np.full(n, 3e37),
+        "ratio_overflow": np.where(np.arange(n) < 2048, 1e-20, 1e25),
+    }
+    for name, m in cases.items():
+        pos = base.copy()
+        pos[:, 3] = m.astype(np.float32)
+        want = _run(engine, pos, dim, pkg.NB_DIRECT_ORDERED)
+        got = _run(engine, pos, dim)
+        assert np.isfinite(want).all(), name
+        assert np.isfinite(got).all(), name
+        scale = np.linalg.norm(want[:, :dim].astype(np.float64), axis=1)
+        err = np.linalg.norm(got[:, :dim].astype(np.float64) - want[:, :dim], axis=1) / np.maximum(scale, 1e-300)
+        assert np.median(err) < 1e-5 and err.max() < 1e-4, (name, np.median(err), err.max())
+
+
+def test_no_hoist_flag_is_the_twelve_operation_sum(engine, pkg):
+    """NB_DIRECT_NO_HOIST: uniform masses, yet the split kernel keeps m_j inside the sum -- the same bits as a system
+    whose masses defeat the hoisting (one odd mass per tile changes nothing else in the arithmetic of other tiles)."""
+    n = 8192
+    pos = pkg.ics.uniform_disk(n, seed=92, z_half_height=3000.0)
+    a = _run(engine, pos, 3, pkg.NB_DIRECT_NO_HOIST)
+    b = _run(engine, pos, 3)
+    field = np.linalg.norm(a[:, :3].astype(np.float64) - b[:, :3]) / np.linalg.norm(b[:, :3].astype(np.float64))
+    assert 0 < field < 1e-6, field     # different rounding (11 vs 12 operations), same sum
+
+
+@pytest.mark.parametrize("dim", [3, 2])
+def test_direct_headline_size(pkg, oracle, dim):
+    """N = 1,048,576 (the size BASELINE.json's metric is quoted on), default mode, NB_DIRECT_NO_HOIST and random masses
+    (no tile hoists), against (i) the FP64 direct sum on 512 sampled targets and (ii) the reference's own kernel, live,
+    on every body.  north_star's bar is 1e-5 relative.  The reference kernel adds 1,048,576 terms into ONE FP32
+    accumulator per target, so it is the reference that sits furthest from FP64 (its own error is asserted here too, for
+    the record); the engine's split sum (8 accumulators per target x source-range partials) is closer.  Asserted:
+    field norm and median body within 1e-5 of FP64 and of the reference kernel; worst sampled body within 5e-5 of the
+    local field scale |a| + (mean |a|) against FP64 (the allowance test_direct_vs_fp64_oracle makes at N = 16,384); 99th
+    percentile against the reference kernel no further than twice what the reference kernel is from FP64 (plus 1e-5).
+    The measured distributions are written to gpurun_out/direct_headline_parity_<dim>d.json."""
+    import torch
+    n = 1 << 20
+    eng = pkg.Engine(0, n)
+    so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
+    ref = None
+    if os.path.exists(so):
+        ref = C.CDLL(so)
+        ref.ref_direct.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float]
+    rng = np.random.default_rng(1234)
+    base = pkg.ics.uniform_disk(n, seed=1, z_half_height=3000.0 if dim == 3 else 0.0)
+    sample = np.arange(0, n, n // 512)[:512]
+    report, failures = {}, []
+    for mass_name in ("uniform", "random"):
+        pos_h = base.copy()
+        if mass_name == "random":
+            pos_h[:, 3] = rng.uniform(1.0e3, 1.4e5, n).astype(np.float32)
+        pos = torch.from_numpy(pos_h).cuda()
+        f64 = np.concatenate([oracle.direct_f64(pos_h, dim, EPS, t0=int(t), nt=1) for t in sample])[:, :dim]
+        mean_a = np.linalg.norm(f64, axis=1).mean()
+        a_ref = None
+        if ref is not None:
+            a_ref_d = torch.zeros(n, 4, device="cuda")
+            assert ref.ref_direct(pos.data_ptr(), a_ref_d.data_ptr(), n, dim, EPS) == 0
+            torch.cuda.synchronize()
+            a_ref = a_ref_d.cpu().numpy()[:, :dim].astype(np.float64)
+        for mode_name, flags in (("default", pkg.NB_DIRECT_AUTO), ("no_hoist", pkg.NB_DIRECT_NO_HOIST)):
+            if mass_name == "random" and mode_name == "no_hoist":
+                continue
+            acc = torch.full((n, 4), 7.0, device="cuda")
+            eng.direct_accel(pos, acc, dim, EPS, flags)
+            torch.cuda.synchronize()
+            got = acc.cpu().numpy()[:, :dim].astype(np.float64)
+            e64 = np.linalg.norm(got[sample] - f64, axis=1) / np.linalg.norm(f64, axis=1)
+            e64_scaled = np.linalg.norm(got[sample] - f64, axis=1) / (np.linalg.norm(f64, axis=1) + mean_a)
+            field64 = np.linalg.norm(got[sample] - f64) / np.linalg.norm(f64)
+            rec = {"vs_fp64": {"field": field64, "median": float(np.median(e64)), "p99": float(np.quantile(e64, 0.99)),
+                               "max": float(e64.max()), "max_scaled": float(e64_scaled.max())}}
+            if not (field64 < 1e-5 and np.median(e64) < 1e-5 and e64_scaled.max() < 5e-5):
+                failures.append((mass_name, mode_name, "fp64", rec["vs_fp64"]))
+            if a_ref is not None:
+                er = np.linalg.norm(got - a_ref, axis=1) / np.linalg.norm(a_ref, axis=1)
+                fieldr = np.linalg.norm(got - a_ref) / np.linalg.norm(a_ref)
+                r64 = np.linalg.norm(a_ref[sample] - f64, axis=1) / np.linalg.norm(f64, axis=1)
+                rec["vs_reference_kernel"] = {"field": fieldr, "median": float(np.median(er)),
+                                              "p99": float(np.quantile(er, 0.99)), "max": float(er.max())}
+                rec["reference_kernel_vs_fp64"] = {"median": float(np.median(r64)), "p99": float(np.quantile(r64, 0.99)),
+                                                   "max": float(r64.max())}
+                if not (fieldr < 1e-5 and np.median(er) < 1e-5 and np.quantile(er, 0.99) <= np.quantile(r64, 0.99) * 2 + 1e-5):
+                    failures.append((mass_name, mode_name, "reference kernel", rec))
+            report[f"{mass_name}/{mode_name}"] = rec
+    eng.close()
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        import json
+        with open(os.path.join(out, f"direct_headline_parity_{dim}d.json"), "w") as f:
+            json.dump(report, f, indent=1)
+    assert not failures, failures

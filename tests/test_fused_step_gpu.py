@@ -1,0 +1,116 @@
+"""nb_bh_step_groups: the stepper's kick + drift fused into the Barnes-Hut walk, on one GPU (in place) and in the
+sharded form (rows in sorted order, scattered back by the next call).  The fused arithmetic is the reference's, so a
+trajectory must equal, BIT FOR BIT, the one the separate kernels give (nb_bh_accel + nb_integrate_substep driven by the
+mirrored IntegrationMethods classes, themselves checked against the reference's expressions in test_integrators_gpu)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+EPS = 1.01
+NAMES = ["Euler_Symplectic_KD", "Euler_Symplectic_DK", "Verlet_DKD", "ForestRuth", "PEFRL"]
+
+
+def _state(pkg, n, seed, vz=False):
+    import torch
+    pos_h = pkg.ics.uniform_disk(n, seed=seed)
+    rng = np.random.default_rng(seed)
+    vel_h = np.zeros((n, 4), np.float32)
+    vel_h[:, :2] = rng.standard_normal((n, 2)).astype(np.float32) * 2.0e4
+    if vz:                       # an R2 run whose bodies carry v_z: the reference's kernels drift z all the same
+        pos_h[:, 2] = rng.standard_normal(n).astype(np.float32) * 100.0
+        vel_h[:, 2] = rng.standard_normal(n).astype(np.float32) * 50.0
+    return torch.from_numpy(pos_h).cuda(), torch.from_numpy(vel_h).cuda()
+
+
+def _classic(pkg, engine, name, pos, vel, dt, steps):
+    sysm = pkg.integrators.ShardedSystem(engine, pos.clone(), vel.clone(), "bh", 2, EPS, 0.5)
+    integ = getattr(pkg.IntegrationMethods, name)()
+    integ.setSystem(sysm)
+    for _ in range(steps):
+        integ.integrate(dt)
+    return sysm.pos, sysm.vel
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_fused_in_place_equals_separate_kernels(engine, pkg, name):
+    import torch
+    n, dt, steps = 20000, 1.0e-3, 3
+    pos, vel = _state(pkg, n, 7, vz=(name == "Verlet_DKD"))
+    want_p, want_v = _classic(pkg, engine, name, pos, vel, dt, steps)
+    p, v = pos.clone(), vel.clone()
+    fused = pkg.integrators.FusedBarnesHut(pkg.Engine(0, n), p, v, name, 0.5, EPS)
+    for _ in range(steps):
+        fused.step(dt)
+    torch.cuda.synchronize()
+    assert torch.equal(p, want_p) and torch.equal(v, want_v)
+    assert fused.force_evaluations == steps * len(pkg.integrators.stepper_program(name, dt)[1])
+
+
+@pytest.mark.parametrize("name,world,n", [("Verlet_DKD", 3, 20000), ("PEFRL", 2, 8192), ("ForestRuth", 4, 5000),
+                                          ("Euler_Symplectic_DK", 8, 12345), ("Euler_Symplectic_KD", 2, 33)])
+def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n):
+    """`world` ranks emulated on one GPU (one engine and one replica of pos / vel each; the all-gather is a
+    concatenation of the ranks' rows): after every step each replica equals the single-GPU trajectory bit for bit,
+    for even and ragged group counts, with v_z carried through."""
+    import torch
+    I = pkg.integrators
+    dt, steps = 1.0e-3, 2
+    pos, vel = _state(pkg, n, 11, vz=True)
+    want_p, want_v = _classic(pkg, engine, name, pos, vel, dt, steps)
+    groups = (n + 31) // 32
+    ranks = []
+    for r in range(world):
+        g0, g1 = pkg.shard.group_bounds(n, world, r)
+        ranks.append(dict(eng=pkg.Engine(0, n), pos=pos.clone(), vel=vel.clone(), g0=g0, g1=g1,
+                          rows_out=torch.full((32 * max(g1 - g0, 1), 4), float("nan"), device="cuda")))
+    rows_all = torch.full((32 * groups, 4), float("nan"), device="cuda")
+    pending = None
+    for _ in range(steps):
+        pre, prog = I.stepper_program(name, dt)
+        for k, (kick, drift) in enumerate(prog):
+            for rk in ranks:
+                rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, rk["g0"], rk["g1"] - rk["g0"],
+                                         pre_drift=pre if k == 0 else (0, 0.0), kick=kick, drift=drift,
+                                         rows_in=rows_all if pending is not None else None,
+                                         prev_drift=pending if pending is not None else (0, 0.0), rows_out=rk["rows_out"])
+            torch.cuda.synchronize()
+            for rk in ranks:                                  # the all-gather
+                rows_all[32 * rk["g0"]:32 * rk["g1"]] = rk["rows_out"][:32 * (rk["g1"] - rk["g0"])]
+            pending = drift
+    for rk in ranks:                                          # materialize
+        rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, 0.0, 0, 0, rows_in=rows_all, prev_drift=pending)
+    torch.cuda.synchronize()
+    for rk in ranks:
+        assert torch.equal(rk["pos"], want_p) and torch.equal(rk["vel"], want_v)
+        rk["eng"].close()
+
+
+def test_fused_stats_match_simulation_stats(engine, pkg):
+    """The per-group sums of the epilogue add up to SimulationStats' moment and kinetic energy (nb_stats, itself the
+    reference's formulae) of the state after the step."""
+    import torch
+    n, dt = 30000, 1.0e-3
+    pos, vel = _state(pkg, n, 13)
+    fused = pkg.integrators.FusedBarnesHut(pkg.Engine(0, n), pos, vel, "Verlet_DKD", 0.5, EPS, stats=True)
+    fused.step(dt)
+    m, k = fused.step(dt, stats=True)
+    want = engine.stats(pos, vel, 2)
+    assert abs(m - want[0]) <= 1e-12 * abs(want[0]) and abs(k - want[1]) <= 1e-12 * abs(want[1]), (m, k, want)
+
+
+def test_fused_step_rejects_what_it_cannot_do(engine, pkg):
+    import torch
+    I = pkg.integrators
+    pos, vel = _state(pkg, 1000, 17)
+    with pytest.raises(pkg.NbodyError):
+        engine.bh_step_groups(pos, vel, 0.5, EPS, 1e-3, 0, 32, kick=(I.KICK_MEAN_F64, 0.0))
+    with pytest.raises(pkg.NbodyError):
+        engine.bh_step_groups(pos, vel, 0.5, EPS, 1e-3, 0, 32, drift=(I.DRIFT_VV_F64, 0.0))
+    with pytest.raises(pkg.NbodyError):
+        engine.bh_step_groups(pos, vel, 0.5, EPS, 1e-3, 0, 33)            # 32 groups only
+    fresh = pkg.Engine(0, 1000)
+    with pytest.raises(pkg.NbodyError):                                    # rows without a previous evaluation
+        fresh.bh_step_groups(pos, vel, 0.5, EPS, 1e-3, 0, 32, rows_in=torch.zeros(1024, 4, device="cuda"))
+    fresh.close()
+    with pytest.raises(ValueError):
+        I.stepper_program("Velocity_Verlet", 1e-3)
