@@ -35,6 +35,15 @@ FLOP_PER_INTERACTION = {3: 20.0, 2: 14.0}   # SURVEY.md section 8d / BASELINE.md
 SM_COUNT, FP32_LANES, MAX_MHZ = 148, 128, 1965.0
 
 
+def shared_config(n, dim, world):
+    """The `config` object both arms print (identical keys and values, so that the driver can match the lines)."""
+    return {"workload": f"direct all-pairs N={n} uniform disk (R{dim}), Leapfrog (Verlet_DKD) step",
+            "n": n, "softening": EPS, "dt": DT,
+            "l2": "GPU arm: flushed between timed iterations (256 MB write); host arm: each sample streams all sources from DRAM",
+            "parallelism": f"target-slice x{world}: targets sharded over {world} GPU(s), one NCCL all-gather of positions per "
+                           f"step; the host arm runs on rank 0's cores only"}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -108,9 +117,8 @@ def run_reference_arm(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"direct all-pairs N={N_BODIES} uniform disk (R3), Leapfrog (Verlet_DKD) step",
-                       "n": N_BODIES, "softening": EPS, "dt": DT,
-                       "sampling": "each step evaluates a bounded slice of the targets against all sources (see cpu_baseline.sample)"},
+            "config": shared_config(N_BODIES, 3, args.gpus),
+            "sampling": "each step evaluates a bounded slice of the targets against all sources (see cpu_baseline.sample)",
             "cpu_baseline": {"value": val, "unit": "interactions/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
@@ -296,6 +304,13 @@ def main():
                 "kernel_ms": kern_ms, "flop_per_interaction": flop,
                 "fp32_pipe_ops_per_interaction": 12 if dim == 3 else 8,
                 "launch": eng.direct_last_launch()}
+    # the same kernel with the mass kept inside the sum for every tile (what any non-uniform mass distribution runs):
+    # north_star's 70 % target is judged on this number; `frac` above profits from the disc's equal masses
+    gen_ms = timed(lambda: eng.direct_accel_slice(pos, begin, count, acc, dim, EPS, pkg.NB_DIRECT_NO_HOIST), 2, 1) / 2
+    roofline["kernel_ms_general_masses"] = gen_ms
+    roofline["frac_general_masses"] = slice_inter * flop / (gen_ms * 1e-3) / 1e12 / peak
+    tiles = pos_h[: (n // 1024) * 1024, 3].reshape(-1, 1024)
+    roofline["hoisted_tile_fraction"] = float((tiles == pos_h[n // 2, 3]).all(axis=1).sum()) / max((n + 1023) // 1024, 1)
     try:   # DRAM traffic of the dominant kernel from the committed ncu --set full capture (per launch)
         tr = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))
         if n == N_BODIES and dim == 3 and world == 1:
@@ -340,10 +355,24 @@ def main():
             ref.ref_direct(pos.data_ptr(), acc_ref.data_ptr(), n, dim, EPS)   # legacy default stream
             torch.cuda.synchronize()
             ref_ms = (time.perf_counter() - t0) * 1e3
+            force()                                                # same positions, this engine (default mode)
+            torch.cuda.synchronize()
+            dd = (acc[:, :dim] - acc_ref[:, :dim]).norm(dim=1) / acc_ref[:, :dim].norm(dim=1)
             extra["reference_cuda_kernel"] = {"interactions_per_s": interactions / (ref_ms * 1e-3), "ms": ref_ms,
-                                              "what": "unmodified src/DirectComputeKernels.cu built for sm_100, same box"}
+                                              "what": "unmodified src/DirectComputeKernels.cu built for sm_100, same box",
+                                              "acc_rel_diff_median": float(dd.median()),
+                                              "acc_rel_diff_p99": float(dd.quantile(0.99)) if n <= (1 << 24) else None,
+                                              "acc_rel_diff_max": float(dd.max()),
+                                              "acc_rel_diff_field": float((acc[:, :dim] - acc_ref[:, :dim]).norm() / acc_ref[:, :dim].norm()),
+                                              "diff_note": "per body, all N bodies, default (hoisted, split) mode vs the reference "
+                                                           "kernel's single FP32 accumulator per target; tests/test_direct_gpu.py::"
+                                                           "test_direct_headline_size holds the FP64 comparison of both"}
+            del acc_ref
 
-    # ---- Barnes-Hut metric (configs[2]: N = 1,048,576, theta = 0.5, one force evaluation per Leapfrog step) ------
+    # ---- Barnes-Hut metric (configs[2]: N = 1,048,576, theta = 0.5, Leapfrog) -------------------------------------------
+    # One step = one complete Verlet_DKD step of the whole system: half drift of all bodies fused into the bounds kernel,
+    # tree build (redundant per GPU), walk of the rank's groups with kick + half drift in its epilogue, and -- sharded --
+    # ONE all-gather of the (x', y', vx', vy') rows (16 B per body).  Nothing is left out of the timed region.
     if not args.skip_bh:
         try:
             nb = N_BODIES
@@ -352,13 +381,38 @@ def main():
             a2 = torch.zeros(nb, 4, device=dev)
             groups = (nb + 31) // 32
             g0, g1 = pkg.shard.group_bounds(nb, world, rank)
+            eng.bh_accel(p2, a2, THETA, EPS)                      # initial state: accelerations -> tangential velocities
+            torch.cuda.synchronize()
+            a2_init = a2.clone()
+            v2 = torch.from_numpy(pkg.ics.disk_velocities(p2_h, a2.cpu().numpy())).to(dev)
+            stepper = pkg.integrators.FusedBarnesHut(eng, p2, v2, "Verlet_DKD", THETA, EPS, world, rank, dist)
+            coll_events = []
+            if world > 1:
+                plain_gather = stepper._gather_rows
 
-            def bh_step():
-                eng.bh_accel_groups(p2, a2, THETA, EPS, g0, g1 - g0)
+                def timed_gather():
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    plain_gather()
+                    e1.record()
+                    coll_events.append((e0, e1))
+                stepper._gather_rows = timed_gather
             ksteps = max(args.steps, 10)
-            bh_ms = timed(bh_step, ksteps, 3) / ksteps
-            bh = {"metric": "BH steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
-                  "ms_per_step": bh_ms, "n": nb, "theta": THETA}
+            bh_ms = timed(lambda: stepper.step(DT, lazy=True), ksteps, 3) / ksteps
+            coll_ms = sum(e0.elapsed_time(e1) for e0, e1 in coll_events[-ksteps:]) / ksteps if coll_events else 0.0
+            stepper.materialize()
+            torch.cuda.synchronize()
+
+            def bh_eval():
+                eng.bh_accel_groups(p2, a2, THETA, EPS, g0, g1 - g0)
+            eval_ms = timed(bh_eval, ksteps, 3) / ksteps
+            bh = {"metric": "BH Leapfrog steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
+                  "ms_per_step": bh_ms, "n": nb, "theta": THETA,
+                  "step": "Verlet_DKD: drift (fused into the bounds kernel) + build + walk with kick/drift epilogue"
+                          + (" + all-gather of 16 B/body rows (NCCL)" if world > 1 else ""),
+                  "collective_ms_per_step": coll_ms, "collective_bytes_per_step": nb * 16 if world > 1 else 0,
+                  "force_evaluation_ms": eval_ms,
+                  "force_evaluation_note": "nb_bh_accel_groups alone on this rank's groups (build + walk, no kick/drift, no collective)"}
             if rank == 0:
                 eng.bh_accel_groups(p2, a2, THETA, EPS, 0, groups, flags=pkg.NB_BH_COUNT_WALK)
                 cnt = eng.bh_last_counters()
@@ -366,7 +420,7 @@ def main():
                 b_walk = 16.0 * (cnt["opened"] + cnt["examined"])
                 bh["counters"] = cnt
                 if world == 1:
-                    gbs = (b_lin + b_walk) / (bh_ms * 1e-3) / 1e9
+                    gbs = (b_lin + b_walk) / (eval_ms * 1e-3) / 1e9
                     peak = 6551.0
                     try:
                         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
@@ -377,8 +431,8 @@ def main():
                                       "traffic": tr.get("bh_walk_n1048576_theta0.5", {}).get("traffic_bytes"),
                                       "traffic_note": "DRAM bytes of the walk kernel (the dominant kernel); the tree is L2-resident",
                                       "algorithmic_bytes": b_lin + b_walk, "b_lin": b_lin,
-                                      "b_walk": b_walk, "peak_source": src,
-                                      "lane_interactions_per_s": cnt["interactions"] / (bh_ms * 1e-3)}
+                                      "b_walk": b_walk, "peak_source": src, "over": "force_evaluation_ms",
+                                      "lane_interactions_per_s": cnt["interactions"] / (eval_ms * 1e-3)}
                     # end to end through the host-buffer entry point
                     p2_pin = torch.from_numpy(p2_h).pin_memory()
                     a2_pin = torch.empty(nb, 4).pin_memory()
@@ -387,15 +441,16 @@ def main():
                     t0 = time.perf_counter()
                     for _ in range(ksteps):
                         eng.bh_accel_host(p2_pin, THETA, EPS, out=a2_pin)
-                    bh["e2e"] = {"value": ksteps / (time.perf_counter() - t0), "unit": "steps/s",
+                    bh["e2e"] = {"value": ksteps / (time.perf_counter() - t0), "unit": "force evaluations/s",
                                  "h2d_bytes_per_step": nb * 16, "d2h_bytes_per_step": nb * 16,
                                  "call": "nb_bh_accel_host"}
                     # theta-error of the result against the FP64 direct sum on a sample of bodies, and the host baseline
+                    # (initial positions: the state the reference's kernels are run on below)
                     if not args.skip_cpu:
                         oracle = graft.load_oracle()
                         sample = np.arange(0, nb, nb // 256)[:256]
                         ref64 = np.concatenate([oracle.direct_f64(p2_h, 2, EPS, t0=int(t), nt=1) for t in sample])[:, :2]
-                        ours = a2[torch.from_numpy(sample).to(dev)].cpu().numpy()[:, :2].astype(np.float64)
+                        ours = a2_init[torch.from_numpy(sample).to(dev)].cpu().numpy()[:, :2].astype(np.float64)
                         err = np.linalg.norm(ours - ref64, axis=1) / np.linalg.norm(ref64, axis=1)
                         bh["theta_error_vs_fp64"] = {"median": float(np.median(err)), "p99": float(np.quantile(err, 0.99)),
                                                      "max": float(err.max()), "sample": 256}
@@ -403,7 +458,7 @@ def main():
                         ob = oracle.bh_accel(p2_h, THETA, EPS)
                         dt_cpu = time.perf_counter() - t0
                         oerr = np.linalg.norm(ob["acc"][sample][:, :2] - ref64, axis=1) / np.linalg.norm(ref64, axis=1)
-                        bh["cpu_baseline"] = {"value": 1.0 / dt_cpu, "unit": "steps/s", "cores": oracle.max_threads(), "kind": "port",
+                        bh["cpu_baseline"] = {"value": 1.0 / dt_cpu, "unit": "force evaluations/s", "cores": oracle.max_threads(), "kind": "port",
                                               "sample": "one full force evaluation at N=1048576 (serial-equivalent tree insert, OpenMP walk)",
                                               "theta_error_median": float(np.median(oerr))}
                     so = os.path.join(ROOT, "oracle", "_ref", "libnbody_ref.so")
@@ -427,13 +482,14 @@ def main():
                         ra = torch.zeros(nb, 4, device=dev)
                         ra[:, :2] = torch.from_numpy(np.load(ref_out)).to(dev)
                         ref_ms = min(tms[1:])
-                        d = (ra[:, :2] - a2[:, :2]).norm(dim=1) / ra[:, :2].norm(dim=1)
+                        d = (ra[:, :2] - a2_init[:, :2]).norm(dim=1) / ra[:, :2].norm(dim=1)
                         ref_err = None
                         if not args.skip_cpu:
                             rr = ra[torch.from_numpy(sample).to(dev)].cpu().numpy()[:, :2].astype(np.float64)
                             e2 = np.linalg.norm(rr - ref64, axis=1) / np.linalg.norm(ref64, axis=1)
                             ref_err = {"median": float(np.median(e2)), "p99": float(np.quantile(e2, 0.99)), "max": float(e2.max())}
-                        bh["reference_cuda_bh"] = {"steps_per_s": 1e3 / ref_ms, "ms": ref_ms, "speedup": ref_ms / bh_ms,
+                        bh["reference_cuda_bh"] = {"force_evaluations_per_s": 1e3 / ref_ms, "ms": ref_ms,
+                                                   "speedup": ref_ms / eval_ms, "speedup_over": "force evaluation vs force evaluation",
                                                    "theta_error_vs_fp64": ref_err,
                                                    "acc_rel_diff_median": float(d.median()),
                                                    "acc_rel_diff_p99": float(d.quantile(0.99)),
@@ -478,10 +534,7 @@ def main():
         line = {"metric": "interactions/s (direct, N=1M)", "value": value, "unit": "interactions/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"direct all-pairs N={n} uniform disk (R{dim}), Leapfrog (Verlet_DKD) step",
-                           "n": n, "softening": EPS, "dt": DT, "l2": "flushed between timed iterations (256 MB write)",
-                           "parallelism": f"target-slice x{world}: targets sharded over {world} GPU(s), one NCCL "
-                                          f"all-gather of positions per step"},
+                "config": shared_config(n, dim, world),
                 "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (launches_force + 2),
                 "roofline": roofline, "cpu_baseline": cpu_baseline}
         line.update(extra)

@@ -27,7 +27,9 @@ constexpr int NT = 256;      // threads per CTA
 constexpr int TILE = 1024;   // sources per pipeline stage (16 KB)
 constexpr int STAGES = 3;
 constexpr int REC_BYTES = 16;
-constexpr int SMEM_BYTES = STAGES * TILE * REC_BYTES + 2 * STAGES * 8;
+constexpr int RING_BYTES = STAGES * TILE * REC_BYTES + 2 * STAGES * 8;
+// + the running totals of the two-level sum: 3 components x PAIRS packed pairs per thread
+constexpr int smem_bytes(int pairs) { return RING_BYTES + 64 + 3 * pairs * NT * 8; }
 
 // UNIFORM: every source of the tile has the reference mass, the factor m_j is hoisted out of the sum (applied once
 // in the epilogue) and an interaction costs 11 instead of 12 FP32-pipe operations.  `mscale` is 1 in the exact
@@ -68,7 +70,9 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
               float4* __restrict__ out,           // acc (jsplit == 1) or partial sums [jsplit][target_count]
               int jsplit,
               const unsigned char* __restrict__ tile_uniform,   // HOIST: 1 where all 1024 masses of a tile equal m_ref
-              const float* __restrict__ mref) {                 // HOIST: [0] = m_ref, [1] = 1/m_ref
+              const float* __restrict__ mref,                   // HOIST: [0] = m_ref, [1] = 1/m_ref
+              int two_level) {   // 1: tile sums are added to running totals in shared memory (chains of 1024 terms);
+                                 // 0: one accumulator per target over the whole source range, the reference's own sum
     float m_ref = 1.f, inv_mref = 1.f;
     bool hoist_on = false;
     if (HOIST) { m_ref = mref[0]; inv_mref = mref[1]; hoist_on = mref[2] != 0.f; }
@@ -76,6 +80,11 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
     const float4* tiles = reinterpret_cast<const float4*>(smem);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * TILE * REC_BYTES);
     uint64_t* empty = full + STAGES;
+    uint64_t* tot = reinterpret_cast<uint64_t*>(smem + RING_BYTES + 64) + threadIdx.x;   // [3 * PAIRS][NT], this thread's column
+    if (two_level) {
+#pragma unroll
+        for (int k = 0; k < 3 * PAIRS; k++) tot[k * NT] = 0ull;
+    }
 
     const int tid = threadIdx.x;
     const int js = blockIdx.y;
@@ -135,6 +144,19 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
         } else {  // ragged last tile of the source array
             for (int j = 0; j < cnt; j++) interact<DIM, PAIRS, false>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, inv_mref, HOIST);
         }
+        if (two_level) {
+            // A target's FP32 sum over 10^5..10^6 sources drifts from the exact sum like a random walk of its rounding
+            // errors (measured at N = 1,048,576: 1.6e-5 of the field norm with one accumulator per 262,144 sources, and
+            // 4e-3 for the reference kernel's single accumulator).  Adding each tile's 1024-term sum to a running total
+            // keeps both chains short; the totals live in shared memory so that no register is held for them.
+#pragma unroll
+            for (int p = 0; p < PAIRS; p++) {
+                tot[(0 * PAIRS + p) * NT] = add2(tot[(0 * PAIRS + p) * NT], AX[p]);
+                tot[(1 * PAIRS + p) * NT] = add2(tot[(1 * PAIRS + p) * NT], AY[p]);
+                if (DIM == 3) tot[(2 * PAIRS + p) * NT] = add2(tot[(2 * PAIRS + p) * NT], AZ[p]);
+                AX[p] = AY[p] = AZ[p] = 0ull;
+            }
+        }
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
         // refill the stage consumed one iteration ago (every warp has had a whole tile of time to leave it)
@@ -152,6 +174,11 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
     float4* dst = out + (size_t)js * target_count;
 #pragma unroll
     for (int p = 0; p < PAIRS; p++) {
+        if (two_level) {
+            AX[p] = tot[(0 * PAIRS + p) * NT];
+            AY[p] = tot[(1 * PAIRS + p) * NT];
+            if (DIM == 3) AZ[p] = tot[(2 * PAIRS + p) * NT];
+        }
         float x0, x1, y0, y1, z0 = 0.f, z1 = 0.f;
         up2(AX[p], x0, x1);
         up2(AY[p], y0, y1);
@@ -240,7 +267,7 @@ __global__ void __launch_bounds__(256) classify_tiles_kernel(const float4* __res
     }
 }
 
-using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int, const unsigned char*, const float*);
+using kernel_fn = void (*)(const float4*, int, int, int, float, float4*, int, const unsigned char*, const float*, int);
 
 struct Variant {
     kernel_fn fn;
@@ -286,9 +313,9 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     const Variant& v = g_variants[hoist ? 1 : 0][dim - 2][pairs == 4 ? 1 : 0];
     int& occupancy = ctx->direct_occ[hoist ? 1 : 0][dim - 2][pairs == 4 ? 1 : 0];
     if (occupancy == 0) {   // first use of this variant on the handle's device (the current device, set above)
-        NB_CUDA(ctx, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        NB_CUDA(ctx, cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(v.pairs)));
         int occ = 0;
-        NB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, NT, SMEM_BYTES));
+        NB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, NT, smem_bytes(v.pairs)));
         occupancy = occ > 0 ? occ : 1;
     }
     const int per_block = NT * 2 * v.pairs;
@@ -346,8 +373,9 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
         launches++;
     }
     dim3 grid(tblocks, jsplit);
-    v.fn<<<grid, NT, SMEM_BYTES, stream>>>(reinterpret_cast<const float4*>(pos), n, target_begin, target_count,
-                                           softening, out, jsplit, flags_d, mref_d);
+    const int two_level = (flags & NB_DIRECT_ORDERED) ? 0 : 1;
+    v.fn<<<grid, NT, smem_bytes(v.pairs), stream>>>(reinterpret_cast<const float4*>(pos), n, target_begin, target_count,
+                                                    softening, out, jsplit, flags_d, mref_d, two_level);
     if (jsplit > 1) {
         reduce_partials_kernel<<<(target_count + 255) / 256, 256, 0, stream>>>(
             reinterpret_cast<const float4*>(ctx->partial), target_count, jsplit, reinterpret_cast<float4*>(acc));
@@ -431,10 +459,10 @@ extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int 
             if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaDeviceGetAttribute", e);
             kernel_fn fns[2] = {(kernel_fn)direct_kernel<2, 2, 3, false>, (kernel_fn)direct_kernel<3, 2, 3, false>};
             for (int k = 0; k < 2; k++) {
-                e = cudaFuncSetAttribute(fns[k], cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+                e = cudaFuncSetAttribute(fns[k], cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(2));
                 if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: cudaFuncSetAttribute", e);
                 int occ = 0;
-                e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fns[k], NT, SMEM_BYTES);
+                e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fns[k], NT, smem_bytes(2));
                 if (e != cudaSuccess) return noalloc_fail(NB_ERR_CUDA, "nb_direct_accel_noalloc: occupancy query", e);
                 d.occupancy[k] = occ > 0 ? occ : 1;
             }
@@ -467,8 +495,8 @@ extern "C" int nb_direct_accel_noalloc(const float* pos, float* acc, int n, int 
 
     cudaStream_t s = (cudaStream_t)stream;
     float4* out = jsplit > 1 ? d.scratch : reinterpret_cast<float4*>(acc);
-    fn<<<dim3(tblocks, jsplit), NT, SMEM_BYTES, s>>>(reinterpret_cast<const float4*>(pos), n, 0, n, softening, out, jsplit,
-                                                     nullptr, nullptr);
+    fn<<<dim3(tblocks, jsplit), NT, smem_bytes(2), s>>>(reinterpret_cast<const float4*>(pos), n, 0, n, softening, out, jsplit,
+                                                        nullptr, nullptr, 1);
     if (jsplit > 1)
         reduce_partials_kernel<<<(n + 255) / 256, 256, 0, s>>>(d.scratch, n, jsplit, reinterpret_cast<float4*>(acc));
     e = cudaGetLastError();

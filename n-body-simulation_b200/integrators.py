@@ -201,7 +201,7 @@ class FusedBarnesHut:
             self.rows_out = self.rows_all[32 * self.g0:32 * self.g1] if self.even else \
                 torch.empty(32 * (self.g1 - self.g0), 4, device=pos.device)
         self.stats_buf = torch.zeros(2 * self.groups, dtype=torch.float64, device=pos.device) if stats else None
-        self.pending = None          # (drift kind, coefficient) of the evaluation whose rows are waiting in rows_all
+        self.pending = None          # ((drift kind, coefficient), dt) of the evaluation whose rows are waiting in rows_all
         self.force_evaluations = 0
 
     def _gather_rows(self):
@@ -215,20 +215,20 @@ class FusedBarnesHut:
     def _group(self, dt, pre, kick, drift, stats):
         e = self.engine
         sharded = self.world > 1
-        rows_in, prev = (self.rows_all, self.pending) if self.pending is not None else (None, (0, 0.0))
+        rows_in, prev = (self.rows_all, self.pending[0]) if self.pending is not None else (None, (0, 0.0))
         e.bh_step_groups(self.pos, self.vel, self.theta, self.eps, dt, self.g0, self.g1 - self.g0, pre_drift=pre, kick=kick,
                          drift=drift, rows_in=rows_in, prev_drift=prev, rows_out=self.rows_out if sharded else None,
                          stats_out=self.stats_buf if stats else None, flags=self.flags)
         self.force_evaluations += 1
         if sharded:
             self._gather_rows()
-            self.pending = drift
+            self.pending = (drift, dt)
 
     def materialize(self):
         """Brings pos / vel (body order) up to date on this rank; a no-op on one GPU."""
         if self.pending is not None:
-            self.engine.bh_step_groups(self.pos, self.vel, self.theta, self.eps, 0.0, 0, 0, rows_in=self.rows_all,
-                                       prev_drift=self.pending, flags=self.flags)
+            self.engine.bh_step_groups(self.pos, self.vel, self.theta, self.eps, self.pending[1], 0, 0, rows_in=self.rows_all,
+                                       prev_drift=self.pending[0], flags=self.flags)
             self.pending = None
 
     def step(self, dt, lazy=False, stats=False):

@@ -78,7 +78,7 @@ def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n):
                 rows_all[32 * rk["g0"]:32 * rk["g1"]] = rk["rows_out"][:32 * (rk["g1"] - rk["g0"])]
             pending = drift
     for rk in ranks:                                          # materialize
-        rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, 0.0, 0, 0, rows_in=rows_all, prev_drift=pending)
+        rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, 0, 0, rows_in=rows_all, prev_drift=pending)
     torch.cuda.synchronize()
     for rk in ranks:
         assert torch.equal(rk["pos"], want_p) and torch.equal(rk["vel"], want_v)
