@@ -115,7 +115,8 @@ class IntegrationMethods:
 class ShardedSystem:
     """State of one rank: replicated positions, slice-local velocities / accelerations, a force method."""
 
-    def __init__(self, engine, pos, vel, method="direct", dim=3, softening=1.01, theta=0.5, world=1, rank=0, dist=None):
+    def __init__(self, engine, pos, vel, method="direct", dim=3, softening=1.01, theta=0.5, world=1, rank=0, dist=None,
+                 direct_flags=0):
         import torch
         from . import shard
         self.engine, self.pos, self.vel = engine, pos, vel
@@ -124,6 +125,7 @@ class ShardedSystem:
         self.begin, self.end = shard.slice_bounds(self.n, world, rank)
         self.count = self.end - self.begin
         self.method, self.dim, self.eps, self.theta = method, dim, softening, theta
+        self.direct_flags = direct_flags
         self.acc = torch.zeros(self.count, 4, device=pos.device)
         self._acc_full = torch.zeros(self.n, 4, device=pos.device) if method == "bh" else None
         self._shard = shard
@@ -133,7 +135,7 @@ class ShardedSystem:
 
     def force(self):
         if self.method == "direct":
-            self.engine.direct_accel_slice(self.pos, self.begin, self.count, self.acc, self.dim, self.eps)
+            self.engine.direct_accel_slice(self.pos, self.begin, self.count, self.acc, self.dim, self.eps, self.direct_flags)
         else:
             # Barnes-Hut shards by groups of the sorted order, not by body slice: walk the rank's groups, then
             # exchange so that every rank holds the accelerations of its own bodies

@@ -71,6 +71,8 @@ int main(int argc, char** argv) {
     auto [m1, k1, p1] = SimulationStats::computeStats(system.space, system.device.pos_mass, system.device.vel, n);
     std::printf("RESULT method=%s n=%d steps=%d E0=%.12e E1=%.12e drift=%.6e moment_drift=%.6e\n", argv[1], n, steps, k0 + p0,
                 k1 + p1, (k1 + p1 - k0 - p0) / (k0 + p0), (m1 - m0) / m0);
+    // the three sums of SimulationStats::computeStats (src/SimulationStats.cu:7-27) before and after, one by one
+    std::printf("STATS M0=%.15e K0=%.15e P0=%.15e M1=%.15e K1=%.15e P1=%.15e\n", m0, k0, p0, m1, k1, p1);
     system.updateHostData();
     FILE* f = std::fopen(argv[5], "wb");
     if (f) {

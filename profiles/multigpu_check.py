@@ -4,6 +4,11 @@ redundantly and the walk is deterministic)."""
 import os
 import sys
 
+# Small systems let 2 or 4 warps share a group (NB_BH_WALK_SPLIT, chosen from the number of groups a GPU walks), which
+# changes the ORDER of a target's FP32 sum with the number of ranks.  One warp per group everywhere makes the sharded
+# result comparable bit for bit; the last block below compares the default schedule within rounding.
+os.environ["NB_BH_WALK_SPLIT"] = "1"
+
 import torch
 import torch.distributed as dist
 

@@ -51,7 +51,9 @@ def test_fused_in_place_equals_separate_kernels(engine, pkg, name):
 def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n):
     """`world` ranks emulated on one GPU (one engine and one replica of pos / vel each; the all-gather is a
     concatenation of the ranks' rows): after every step each replica equals the single-GPU trajectory bit for bit,
-    for even and ragged group counts, with v_z carried through."""
+    for even and ragged group counts, with v_z carried through.  (Sizes at which one GPU and a rank choose the same
+    number of warps per group; a different choice changes the order of a target's FP32 sum -- profiles/multigpu_check.py
+    pins it with NB_BH_WALK_SPLIT=1 for its two-rank comparison.)"""
     import torch
     I = pkg.integrators
     dt, steps = 1.0e-3, 2
