@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
+# NB_LIB: another build of the same library (profiles/build_variant.sh: tuning experiments side by side in one process tree)
+_LIB_PATH = os.environ.get("NB_LIB") or os.path.join(_HERE, "libnbody_b200.so")
 _lib = None
 
 NB_OK = 0

@@ -250,10 +250,28 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
     const float4 bb = *bounds;
     for (int i = blockIdx.x * KEYS_PER_BLOCK + threadIdx.x; i < min(n, (blockIdx.x + 1) * KEYS_PER_BLOCK); i += KEYS_THREADS) {
         const float4 p = pos[i];
-        uint32_t k32 = 0;
+        // tree-path key: 32 levels of the '>=' descent.  The SFC key's strict '>' (:212-231) takes the other branch only
+        // where a coordinate EQUALS a midpoint; away from such hits both bisect the same intervals and the SFC code
+        // equals the tree digit (path ^ 2), so the SFC key is the upper half of the tree key.
+        uint64_t k64 = 0;
+        bool hit = false;
         {
+            float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
+#pragma unroll 8
+            for (int lev = 0; lev < MAX_LEVEL; lev++) {
+                unsigned path = 0;
+                const float midX = (maxX + minX) * 0.5f;
+                if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
+                const float midY = (maxY + minY) * 0.5f;
+                if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
+                if (lev < 16) hit |= (p.x == midX) | (p.y == midY);
+                k64 |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
+            }
+        }
+        uint32_t k32 = (uint32_t)(k64 >> 32);
+        if (hit) {   // a body exactly on a cell edge of the first 16 levels: the reference's own loop
+            k32 = 0;
             float l = bb.x, r = bb.z, b = bb.y, t = bb.w;
-#pragma unroll
             for (int s = 30; s >= 0; s -= 2) {
                 const float midX = (r + l) * 0.5f;
                 const float midY = (t + b) * 0.5f;
@@ -266,19 +284,6 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
                     if (p.y > midY) { b = midY; }
                     else            { t = midY; k32 |= 2u << s; }
                 }
-            }
-        }
-        uint64_t k64 = 0;
-        {
-            float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
-#pragma unroll 8
-            for (int lev = 0; lev < MAX_LEVEL; lev++) {
-                unsigned path = 0;
-                const float midX = (maxX + minX) * 0.5f;
-                if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
-                const float midY = (maxY + minY) * 0.5f;
-                if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
-                k64 |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
             }
         }
         key32[i] = k32;
@@ -310,13 +315,16 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
 // a device flag switches on eight conditional passes (a full LSD sort from the current order -- ties keep their
 // order, so the result is again the stable sort) that otherwise return at once.
 // ------------------------------------------------------------------------------------------------------
-constexpr int HYBRID_LOW_BITS = 24;      // bits left to the fix-up
+// bits left to the fix-up: 24 (five passes over 20 levels), or 32 (four passes over 16 levels) for systems small enough
+// that few bodies share a level-16 cell (a uniform million-body disc: a few hundred)
+inline int hybrid_low_bits(int n) { return n <= (1 << 21) ? 32 : 24; }
 constexpr int FIX_CAP = 2048;            // members of short-of-sorted runs one block can repair
 constexpr int N_SLOTS = N_DIGITS + 8;    // ticket / status areas: 12 regular passes + 8 conditional ones
 constexpr int FIX_COUNT_WORD = 32, FIX_FLAG_WORD = 33;   // in the 64-word ticket area (cleared with it)
 
 __global__ void __launch_bounds__(256) mark_runs_kernel(const uint64_t* __restrict__ K, int n, int32_t* __restrict__ work,
-                                                       uint32_t* __restrict__ count, uint32_t* __restrict__ full_sort) {
+                                                       uint32_t* __restrict__ count, uint32_t* __restrict__ full_sort,
+                                                       const int HYBRID_LOW_BITS) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool f = false;
     if (i < n) {
@@ -726,6 +734,10 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
 // :431-433); rejected nodes go to a LIFO of node ids that is popped eight nodes (32 child records) at a time.
 // Summation order differs from the depth-first walk (FP32 rounding only).
 // ------------------------------------------------------------------------------------------------------
+#ifndef NB_WALK_UNROLL
+#define NB_WALK_UNROLL 2
+#endif
+constexpr int WL_UNROLL = NB_WALK_UNROLL;   // packed pairs per iteration of the list evaluation
 constexpr int WL_WARPS = 4;
 constexpr int WL_QCAP = 1024;   // node ids per group (measured peak at N = 1M, theta = 0.5: see bench counters)
 constexpr int WL_LCAP = 64;     // pending accepted records per group
@@ -820,7 +832,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
         if ((lcount & 1) && lane == 0) append(lcount, FAR_AWAY, FAR_AWAY, 0.f);   // odd count: a massless partner
         __syncwarp();
         const int pairs = (lcount + 1) >> 1;
-#pragma unroll 2
+#pragma unroll WL_UNROLL
         for (int k = 0; k < pairs; k++) {
             const ulonglong2 c = reinterpret_cast<const ulonglong2*>(lxy)[k];     // (cx0, cx1) (cy0, cy1)
             const uint64_t m2 = reinterpret_cast<const uint64_t*>(lm)[k];          // (m0, m1)
@@ -1243,10 +1255,12 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
             uint32_t* const fix_count = st->os_ticket + FIX_COUNT_WORD;
             uint32_t* const fix_flag = st->os_ticket + FIX_FLAG_WORD;
             int sel = 0;
+            const int low_bits = hybrid_low_bits(n);
             rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n,
-                                      HYBRID_LOW_BITS, 64, 4, 4 + HYBRID_LOW_BITS / 8, true, 0, nullptr, &sel, stream);
+                                      low_bits, 64, 4, 4 + low_bits / 8, true, 0, nullptr, &sel, stream);
             if (!rc) {
-                mark_runs_kernel<<<(n + 255) / 256, 256, 0, stream>>>(st->key64[sel], n, st->fix_work, fix_count, fix_flag);
+                mark_runs_kernel<<<(n + 255) / 256, 256, 0, stream>>>(st->key64[sel], n, st->fix_work, fix_count, fix_flag,
+                                                                      low_bits);
                 fix_runs_kernel<<<1, 1024, 0, stream>>>(st->key64[sel], st->idx64[sel], st->fix_work, fix_count, fix_flag,
                                                         st->d_full_flag);
                 rc = radix_sort<uint64_t>(ctx, st->ghist, st->os_status, st->os_stride, st->os_ticket, st->key64, st->idx64, n, 0,

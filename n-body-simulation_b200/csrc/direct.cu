@@ -23,9 +23,24 @@
 
 namespace {
 
+// compile-time tuning knobs (profiles/build_variant.sh); the defaults are the measured best
+#ifndef NB_DIRECT_TILE
+#define NB_DIRECT_TILE 1024
+#endif
+#ifndef NB_DIRECT_STAGES
+#define NB_DIRECT_STAGES 3
+#endif
+#ifndef NB_DIRECT_UNROLL
+#define NB_DIRECT_UNROLL 4
+#endif
+#ifndef NB_DIRECT_BIG_PAIRS
+#define NB_DIRECT_BIG_PAIRS 4
+#endif
 constexpr int NT = 256;      // threads per CTA
-constexpr int TILE = 1024;   // sources per pipeline stage (16 KB)
-constexpr int STAGES = 3;
+constexpr int TILE = NB_DIRECT_TILE;   // sources per pipeline stage (16 KB)
+constexpr int STAGES = NB_DIRECT_STAGES;
+constexpr int J_UNROLL = NB_DIRECT_UNROLL;
+constexpr int BIG = NB_DIRECT_BIG_PAIRS;   // targets per thread / 2 of the variant used when targets alone fill the GPU
 constexpr int REC_BYTES = 16;
 constexpr int RING_BYTES = STAGES * TILE * REC_BYTES + 2 * STAGES * 8;
 // + the running totals of the two-level sum: 3 components x PAIRS packed pairs per thread
@@ -136,10 +151,10 @@ direct_kernel(const float4* __restrict__ pos,     // all n bodies: sources, and 
         const float4* tp = tiles + s * TILE;
         const int cnt = tile_count(tile0 + it);
         if (HOIST && hoist_on && cnt == TILE && tile_uniform[tile0 + it]) {
-#pragma unroll 4
+#pragma unroll J_UNROLL
             for (int j = 0; j < TILE; j++) interact<DIM, PAIRS, true>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, 1.f, false);
         } else if (cnt == TILE) {
-#pragma unroll 4
+#pragma unroll J_UNROLL
             for (int j = 0; j < TILE; j++) interact<DIM, PAIRS, false>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, inv_mref, HOIST);
         } else {  // ragged last tile of the source array
             for (int j = 0; j < cnt; j++) interact<DIM, PAIRS, false>(tp[j], BX, BY, BZ, AX, AY, AZ, E2, inv_mref, HOIST);
@@ -275,10 +290,10 @@ struct Variant {
 };
 
 const Variant g_variants[2][2][2] = {   // [hoist][dim - 2][pairs == 4]; per-device state lives in nb_context::direct_occ
-    {{{direct_kernel<2, 2, 3, false>, 2}, {direct_kernel<2, 4, 2, false>, 4}},
-     {{direct_kernel<3, 2, 3, false>, 2}, {direct_kernel<3, 4, 2, false>, 4}}},
-    {{{direct_kernel<2, 2, 3, true>, 2}, {direct_kernel<2, 4, 2, true>, 4}},
-     {{direct_kernel<3, 2, 3, true>, 2}, {direct_kernel<3, 4, 2, true>, 4}}},
+    {{{direct_kernel<2, 2, 3, false>, 2}, {direct_kernel<2, BIG, 2, false>, BIG}},
+     {{direct_kernel<3, 2, 3, false>, 2}, {direct_kernel<3, BIG, 2, false>, BIG}}},
+    {{{direct_kernel<2, 2, 3, true>, 2}, {direct_kernel<2, BIG, 2, true>, BIG}},
+     {{direct_kernel<3, 2, 3, true>, 2}, {direct_kernel<3, BIG, 2, true>, BIG}}},
 };
 
 int env_int(const char* name, int dflt) {
