@@ -89,11 +89,11 @@ struct nb_bh_state {
     // into a CUDA graph and replayed while the call's arguments stay the same
     struct GraphKey {
         const float* pos; float* acc; int n, flags, group_begin, group_count, accumulate; float theta, eps; bool sort_full;
-        int qcap;
+        int qcap, sched;
         bool operator==(const GraphKey& o) const {
             return pos == o.pos && acc == o.acc && n == o.n && flags == o.flags && group_begin == o.group_begin &&
                    group_count == o.group_count && accumulate == o.accumulate && theta == o.theta && eps == o.eps &&
-                   sort_full == o.sort_full && qcap == o.qcap;
+                   sort_full == o.sort_full && qcap == o.qcap && sched == o.sched;
         }
     };
     GraphKey graph_key{};
@@ -250,28 +250,10 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
     const float4 bb = *bounds;
     for (int i = blockIdx.x * KEYS_PER_BLOCK + threadIdx.x; i < min(n, (blockIdx.x + 1) * KEYS_PER_BLOCK); i += KEYS_THREADS) {
         const float4 p = pos[i];
-        // tree-path key: 32 levels of the '>=' descent.  The SFC key's strict '>' (:212-231) takes the other branch only
-        // where a coordinate EQUALS a midpoint; away from such hits both bisect the same intervals and the SFC code
-        // equals the tree digit (path ^ 2), so the SFC key is the upper half of the tree key.
-        uint64_t k64 = 0;
-        bool hit = false;
+        uint32_t k32 = 0;
         {
-            float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
-#pragma unroll 8
-            for (int lev = 0; lev < MAX_LEVEL; lev++) {
-                unsigned path = 0;
-                const float midX = (maxX + minX) * 0.5f;
-                if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
-                const float midY = (maxY + minY) * 0.5f;
-                if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
-                if (lev < 16) hit |= (p.x == midX) | (p.y == midY);
-                k64 |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
-            }
-        }
-        uint32_t k32 = (uint32_t)(k64 >> 32);
-        if (hit) {   // a body exactly on a cell edge of the first 16 levels: the reference's own loop
-            k32 = 0;
             float l = bb.x, r = bb.z, b = bb.y, t = bb.w;
+#pragma unroll
             for (int s = 30; s >= 0; s -= 2) {
                 const float midX = (r + l) * 0.5f;
                 const float midY = (t + b) * 0.5f;
@@ -284,6 +266,19 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
                     if (p.y > midY) { b = midY; }
                     else            { t = midY; k32 |= 2u << s; }
                 }
+            }
+        }
+        uint64_t k64 = 0;
+        {
+            float minX = bb.x, maxX = bb.z, minY = bb.y, maxY = bb.w;
+#pragma unroll 8
+            for (int lev = 0; lev < MAX_LEVEL; lev++) {
+                unsigned path = 0;
+                const float midX = (maxX + minX) * 0.5f;
+                if (p.x >= midX) { minX = midX; path += 1; } else { maxX = midX; }
+                const float midY = (maxY + minY) * 0.5f;
+                if (p.y >= midY) { minY = midY; path += 2; } else { maxY = midY; }
+                k64 |= (uint64_t)(path ^ 2u) << (62 - 2 * lev);
             }
         }
         key32[i] = k32;
@@ -315,9 +310,9 @@ __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __rest
 // a device flag switches on eight conditional passes (a full LSD sort from the current order -- ties keep their
 // order, so the result is again the stable sort) that otherwise return at once.
 // ------------------------------------------------------------------------------------------------------
-// bits left to the fix-up: 24 (five passes over 20 levels), or 32 (four passes over 16 levels) for systems small enough
-// that few bodies share a level-16 cell (a uniform million-body disc: a few hundred)
-inline int hybrid_low_bits(int n) { return n <= (1 << 21) ? 32 : 24; }
+// bits left to the fix-up: 24 (five passes over 20 levels).  Measured at N = 1M: four passes (32 bits left) save one 23 us
+// pass but put 1300 bodies instead of a handful into the one-block repair sort, which then takes 37 us instead of 5
+inline int hybrid_low_bits(int) { return 24; }
 constexpr int FIX_CAP = 2048;            // members of short-of-sorted runs one block can repair
 constexpr int N_SLOTS = N_DIGITS + 8;    // ticket / status areas: 12 regular passes + 8 conditional ones
 constexpr int FIX_COUNT_WORD = 32, FIX_FLAG_WORD = 33;   // in the 64-word ticket area (cleared with it)
@@ -735,7 +730,7 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
 // Summation order differs from the depth-first walk (FP32 rounding only).
 // ------------------------------------------------------------------------------------------------------
 #ifndef NB_WALK_UNROLL
-#define NB_WALK_UNROLL 2
+#define NB_WALK_UNROLL 8
 #endif
 constexpr int WL_UNROLL = NB_WALK_UNROLL;   // packed pairs per iteration of the list evaluation
 constexpr int WL_WARPS = 4;
@@ -1301,6 +1296,10 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
     return NB_OK;
 }
 
+// schedule switch (tests, measurements), read at every call: NB_BH_WALK_SPLIT = warps per group (1, 2, 4; default by
+// the number of groups)
+int walk_forced_split() { const char* v = getenv("NB_BH_WALK_SPLIT"); return v ? atoi(v) : 0; }
+
 // NB_BH_WALK_QCAP (tests): a smaller queue threshold sends groups down the depth-first path early
 int walk_qcap() {
     int qcap = WL_QCAP - WL_DFS_ROOM;
@@ -1332,7 +1331,7 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
                                                                       st->root_rec, eps, group_begin, group_count, acc, st->counters);
     } else {
         // fewer groups than it takes to keep the SMs busy (16 warps each): 2 or 4 warps share a group
-        static const int forced_split = [] { const char* v = getenv("NB_BH_WALK_SPLIT"); return v ? atoi(v) : 0; }();
+        const int forced_split = walk_forced_split();
         const int busy = ctx->sm_count * 16;
         int split = group_count >= busy ? 1 : (2 * group_count >= busy ? 2 : 4);
         if (forced_split == 1 || forced_split == 2 || forced_split == 4) split = forced_split;
@@ -1402,7 +1401,7 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     nb_bh_state* st = ctx->bh;
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
     const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening, st->sort_full,
-                                      walk_qcap()};
+                                      walk_qcap(), walk_forced_split()};
     if (!st->graph_exec || !(st->graph_key == key)) {
         if (st->graph_exec) { cudaGraphExecDestroy(st->graph_exec); st->graph_exec = nullptr; }
         if (!st->capture_stream) NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->capture_stream, cudaStreamNonBlocking));

@@ -31,10 +31,10 @@ namespace {
 #define NB_DIRECT_STAGES 3
 #endif
 #ifndef NB_DIRECT_UNROLL
-#define NB_DIRECT_UNROLL 4
+#define NB_DIRECT_UNROLL 16
 #endif
 #ifndef NB_DIRECT_BIG_PAIRS
-#define NB_DIRECT_BIG_PAIRS 4
+#define NB_DIRECT_BIG_PAIRS 3
 #endif
 constexpr int NT = 256;      // threads per CTA
 constexpr int TILE = NB_DIRECT_TILE;   // sources per pipeline stage (16 KB)
@@ -289,7 +289,7 @@ struct Variant {
     int pairs;
 };
 
-const Variant g_variants[2][2][2] = {   // [hoist][dim - 2][pairs == 4]; per-device state lives in nb_context::direct_occ
+const Variant g_variants[2][2][2] = {   // [hoist][dim - 2][big]; per-device state lives in nb_context::direct_occ
     {{{direct_kernel<2, 2, 3, false>, 2}, {direct_kernel<2, BIG, 2, false>, BIG}},
      {{direct_kernel<3, 2, 3, false>, 2}, {direct_kernel<3, BIG, 2, false>, BIG}}},
     {{{direct_kernel<2, 2, 3, true>, 2}, {direct_kernel<2, BIG, 2, true>, BIG}},
@@ -318,10 +318,10 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     const int ntiles = (n + TILE - 1) / TILE;
     int rc = NB_OK;
 
-    // choose the register blocking: 8 targets/thread when there are enough targets to fill the GPU with
-    // them, else 4 (finer granularity); NB_DIRECT_PAIRS overrides for tuning.
+    // choose the register blocking: 2 * BIG targets/thread when there are enough targets to fill the GPU with
+    // them, else 4 (finer granularity); NB_DIRECT_PAIRS (2 = small, 4 = big) overrides for tuning.
     int pairs = env_int("NB_DIRECT_PAIRS", 0);
-    if (pairs != 2 && pairs != 4) pairs = (target_count >= ctx->sm_count * 2 * NT * 8) ? 4 : 2;
+    if (pairs != 2 && pairs != 4) pairs = (target_count >= ctx->sm_count * 2 * NT * 2 * BIG) ? 4 : 2;
     // Hoisting the common mass out of the sum changes the rounding (not the order) of the sum: exact mode keeps
     // the reference arithmetic; NB_DIRECT_NO_HOIST switches it off for tuning.
     const bool hoist = !(flags & (NB_DIRECT_ORDERED | NB_DIRECT_NO_HOIST)) && env_int("NB_DIRECT_NO_HOIST", 0) == 0;

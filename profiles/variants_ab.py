@@ -46,6 +46,9 @@ def worker():
         out["direct2d_general_ms"] = timed(lambda: eng.direct_accel(pos2, acc, 2, 1.01, pkg.NB_DIRECT_NO_HOIST), 3, 1)
     if only != "direct":
         out["bh_eval_ms"] = timed(lambda: eng.bh_accel(pos2, acc, 0.5, 1.01), 20, 3)
+        cc = pkg.ics.cold_collapse_late(n, seed=2)
+        posc = torch.from_numpy(cc).cuda()
+        out["bh_eval_cold_collapse_ms"] = timed(lambda: eng.bh_accel(posc, acc, 0.5, 1.01), 20, 3)
     print("AB " + json.dumps(out), flush=True)
 
 

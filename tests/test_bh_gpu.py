@@ -71,9 +71,18 @@ def test_integer_stages_bit_exact(engine, pkg, oracle, case):
     assert np.array_equal(st["tree_keys"], oracle.bh_tree_keys(pos, b))
 
 
+SCHEDULES = {"default": {}, "one_warp_per_group": {"NB_BH_WALK_SPLIT": "1"}}
+
+
+@pytest.mark.parametrize("schedule", ["default", "one_warp_per_group"])
 @pytest.mark.parametrize("case", CASES)
-def test_tree_topology_and_accelerations(engine, pkg, oracle, case):
+def test_tree_topology_and_accelerations(engine, pkg, oracle, case, schedule, monkeypatch):
+    """Both walk schedules -- 2 or 4 warps per group (small systems, the default at these sizes) and one warp per group
+    (what systems of 75,000+ bodies run) -- must produce the reference's accepted set: the lane-interaction count equals
+    the oracle walk's."""
     import torch
+    for k, v in SCHEDULES[schedule].items():
+        monkeypatch.setenv(k, v)
     pos = _cases(pkg)[case]
     n = pos.shape[0]
     theta = 0.5
@@ -153,8 +162,12 @@ def test_small_theta_converges_to_direct_sum(engine, pkg, oracle):
     assert _rel(acc.cpu().numpy(), d).max() < 5e-5
 
 
-def test_group_slices_tile_the_full_result(engine, pkg):
+@pytest.mark.parametrize("schedule", ["default", "one_warp_per_group"])
+def test_group_slices_tile_the_full_result(engine, pkg, schedule, monkeypatch):
+    """Any partition of the groups reproduces the full evaluation bit for bit (given the same number of warps per group)."""
     import torch
+    for k, v in SCHEDULES[schedule].items():
+        monkeypatch.setenv(k, v)
     n = 10000
     pos = _dev(pkg.ics.uniform_disk(n, seed=43))
     full = torch.zeros(n, 4, device="cuda")
@@ -317,13 +330,16 @@ def test_dense_system_same_result_on_every_sort_path(pkg):
         eng.close()
 
 
+@pytest.mark.parametrize("schedule", ["default", "one_warp_per_group"])
 @pytest.mark.parametrize("case", ["disk_8192", "clustered_8192", "duplicates_3000", "dense_knot_6000"])
-def test_full_queue_finishes_depth_first(engine, pkg, oracle, case, monkeypatch):
+def test_full_queue_finishes_depth_first(engine, pkg, oracle, case, schedule, monkeypatch):
     """A group whose node queue fills up finishes its walk in depth-first order instead of dropping nodes (the
     reference's 64-entry stack overflows silently, src/BarnesHutKernels.cu:388).  NB_BH_WALK_QCAP lowers the threshold
     so that nearly every group takes that path: same interaction count, same accelerations up to the order of the
     FP32 sum, and the status bit says that it happened."""
     import torch
+    for k, v in SCHEDULES[schedule].items():
+        monkeypatch.setenv(k, v)
     pos = _cases(pkg)[case]
     n = pos.shape[0]
     dpos = _dev(pos)
