@@ -270,6 +270,30 @@ typedef struct nb_bh_step {
 } nb_bh_step;
 int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_bh_step* step, void* stream);
 
+/* The same for the direct sum, on a target slice: optional drift of the slice's bodies (done by the kernel that classifies
+ * the source tiles), the force, and the kick + drift of the slice's bodies (done by the kernel that adds up the source-range
+ * partial sums: positions may only move once every block has read them as sources).  3 launches per sub-step instead of 5;
+ * for n <= 65,536 (launch-bound) the launches are captured into a CUDA graph once and replayed while the arguments stay
+ * the same.  pos: device float4[n], read and written; vel: device float4[target_count], slice-local; acc_out (optional,
+ * slice-local) receives the accelerations; stats_out (optional, device double[2 ceil(target_count/256)]): per block of 256
+ * targets sum m|v| and sum m v^2/2 of the kicked velocities (src/SimulationStats.cu:29-60).  A sharded run drifts with
+ * nb_integrate_substep, all-gathers the positions, and passes pre_drift_kind = NB_DRIFT_NONE here.  NB_KICK_MEAN_F64 is not
+ * available (it needs two accelerations).  No counterpart in the reference (separate launches, one GPU). */
+typedef struct nb_direct_step {
+    float softening, dt;
+    int dim, flags;            /* NB_DIRECT_* */
+    int target_begin, target_count;
+    int pre_drift_kind;
+    double pre_drift_coef;
+    int kick_kind;
+    double kick_coef;
+    int drift_kind;
+    double drift_coef;
+    float* acc_out;
+    double* stats_out;
+} nb_direct_step;
+int nb_direct_step_slice(nb_context* ctx, float* pos, float* vel, int n, const nb_direct_step* step, void* stream);
+
 /* ---- diagnostics (callers of the path) ------------------------------------- */
 
 /* SimulationStats::computeStats (src/SimulationStats.cu:7-27) for the bodies [target_begin, target_begin +

@@ -24,7 +24,7 @@ NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS, NB_BH_COUNT_WALK = 0, 1, 0x100
 ABI_SYMBOLS = [
     "nb_create", "nb_destroy", "nb_last_error", "nb_device_info",
     "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_accel_noalloc",
-    "nb_direct_last_launch",
+    "nb_direct_last_launch", "nb_direct_step_slice",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_bh_build_info", "nb_bh_step_groups", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
     "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities",
@@ -34,6 +34,16 @@ ABI_SYMBOLS = [
 
 class NbodyError(RuntimeError):
     pass
+
+
+class DirectStep(C.Structure):
+    """struct nb_direct_step of include/nbody_b200.h."""
+    _fields_ = [("softening", C.c_float), ("dt", C.c_float), ("dim", C.c_int), ("flags", C.c_int),
+                ("target_begin", C.c_int), ("target_count", C.c_int),
+                ("pre_drift_kind", C.c_int), ("pre_drift_coef", C.c_double),
+                ("kick_kind", C.c_int), ("kick_coef", C.c_double),
+                ("drift_kind", C.c_int), ("drift_coef", C.c_double),
+                ("acc_out", C.c_void_p), ("stats_out", C.c_void_p)]
 
 
 class BHStep(C.Structure):
@@ -69,6 +79,7 @@ def lib():
         L.nb_direct_accel_slice.argtypes = [vp, vp, i, i, i, vp, i, f, i, vp]
         L.nb_direct_accel_host.argtypes = [vp, vp, vp, i, i, f, i]
         L.nb_direct_last_launch.argtypes = [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i)]
+        L.nb_direct_step_slice.argtypes = [vp, vp, vp, i, C.POINTER(DirectStep), vp]
         L.nb_bh_accel.argtypes = [vp, vp, vp, i, f, f, i, vp]
         L.nb_bh_accel_groups.argtypes = [vp, vp, vp, i, f, f, i, i, i, vp]
         L.nb_bh_accel_host.argtypes = [vp, vp, vp, i, f, f, i]
@@ -155,6 +166,18 @@ class Engine:
         o, _ = _host_ptr(out)
         self._check(lib().nb_direct_accel_host(self._h, p, o, n, dim, softening, flags), "nb_direct_accel_host")
         return out
+
+    def direct_step_slice(self, pos, vel, dim, softening, dt, target_begin, target_count, pre_drift=(0, 0.0), kick=(0, 0.0),
+                          drift=(0, 0.0), acc_out=None, stats_out=None, flags=NB_DIRECT_AUTO, stream=None):
+        """One [pre-drift; force; kick; drift] group of a stepper with the kick and drift fused into the kernels of the
+        direct sum (nb_direct_step_slice).  pos: CUDA float32 [n,4]; vel: [target_count,4], slice-local."""
+        n = pos.shape[0]
+        _check_tensor(pos, n), _check_tensor(vel, target_count)
+        st = DirectStep(softening, dt, dim, flags, target_begin, target_count, pre_drift[0], pre_drift[1], kick[0], kick[1],
+                        drift[0], drift[1], acc_out.data_ptr() if acc_out is not None else None,
+                        stats_out.data_ptr() if stats_out is not None else None)
+        self._check(lib().nb_direct_step_slice(self._h, pos.data_ptr(), vel.data_ptr(), n, C.byref(st), _stream_ptr(stream)),
+                    "nb_direct_step_slice")
 
     def direct_last_launch(self):
         a, b, c = C.c_int(), C.c_int(), C.c_int()

@@ -44,6 +44,8 @@ int nb_destroy(nb_context* ctx) {
     cudaDeviceSynchronize();
     nb_bh_destroy(ctx);
     nb_bh3_destroy(ctx);
+    if (ctx->direct_graph) cudaGraphExecDestroy((cudaGraphExec_t)ctx->direct_graph);
+    if (ctx->direct_capture_stream) cudaStreamDestroy((cudaStream_t)ctx->direct_capture_stream);
     if (ctx->partial) cudaFree(ctx->partial);
     if (ctx->tile_flags) cudaFree(ctx->tile_flags);
     if (ctx->stats) cudaFree(ctx->stats);

@@ -32,6 +32,11 @@ struct nb_context {
     // made here yet (cudaFuncSetAttribute is per device: a process-wide cache would skip it on a second GPU)
     int direct_occ[2][2][2] = {};
 
+    // nb_direct_step_slice at launch-bound sizes: one captured graph, replayed while the arguments stay the same
+    void* direct_graph = nullptr;            // cudaGraphExec_t
+    void* direct_capture_stream = nullptr;   // cudaStream_t
+    unsigned char direct_graph_key[160] = {0};
+
     nb_bh_state* bh = nullptr;
     nb_bh3_state* bh3 = nullptr;
     size_t bh_bytes = 0, bh3_bytes = 0;   // device memory held by the two Barnes-Hut states

@@ -20,6 +20,9 @@
 // Measured dispatch model (profiles/README.md): an SM sub-partition spends 2 cycles per packed FP32x2
 // instruction, ~2 per MUFU and 1 per anything else, so the loop is kept free of everything else.
 #include "common.cuh"
+#include "integrate.cuh"
+
+#include <cstring>
 
 namespace {
 
@@ -227,6 +230,82 @@ __global__ void zero_acc_kernel(float4* acc, int n) {
     if (i < n) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+// nb_direct_step_slice: the stepper's kernels around the force evaluation ride on the kernels that run anyway.
+//   pre  : drift of the slice's bodies before the force (pos += f(vel)), done by the tile-classification kernel (or a
+//          kernel of its own when no classification runs); only meaningful when no exchange of positions has to
+//          happen between the drift and the force, i.e. on one GPU
+//   post : kick + drift of the slice's bodies, done by the kernel that adds up the source-range partial sums --
+//          positions may only move once EVERY block has finished reading them as sources, so never by the force kernel
+struct DirectFused {
+    float4* pos_rw;      // all n bodies
+    float4* vel;         // slice-local
+    int begin, count;
+    SubstepArgs pre, post;
+    float4* acc_out;     // optional, slice-local
+    double* stats;       // optional: per 256-target block (sum m|v|, sum m v^2 / 2) of the kicked velocities
+    int dim;
+};
+
+__global__ void __launch_bounds__(256) pre_drift_kernel(const DirectFused f) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= f.count) return;
+    float4 p = f.pos_rw[f.begin + i];
+    const float4 v = f.vel[i];
+    p.x = drift1g(f.pre, p.x, v.x, 0.f);
+    p.y = drift1g(f.pre, p.y, v.y, 0.f);
+    p.z = drift1g(f.pre, p.z, v.z, 0.f);
+    f.pos_rw[f.begin + i] = p;
+}
+
+// acc = partial[0] + partial[1] + ... (fixed order), then the stepper's kick and drift on the same thread's body
+__global__ void __launch_bounds__(256) reduce_step_kernel(const float4* __restrict__ partial, int jsplit, const DirectFused f) {
+    __shared__ double red[2][8];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < f.count;
+    double lm = 0.0, lk = 0.0;
+    if (valid) {
+        float4 a = partial[i];
+        for (int k = 1; k < jsplit; k++) {
+            const float4 w = partial[(size_t)k * f.count + i];
+            a.x += w.x;
+            a.y += w.y;
+            a.z += w.z;
+        }
+        a.w = 0.f;
+        float4 v = f.vel[i];
+        float4 p = f.pos_rw[f.begin + i];
+        v.x = kick1(f.post, v.x, a.x, 0.f);
+        v.y = kick1(f.post, v.y, a.y, 0.f);
+        v.z = kick1(f.post, v.z, a.z, 0.f);
+        p.x = drift1g(f.post, p.x, v.x, a.x);
+        p.y = drift1g(f.post, p.y, v.y, a.y);
+        p.z = drift1g(f.post, p.z, v.z, a.z);
+        if (f.post.kick != NB_KICK_NONE) f.vel[i] = v;
+        if (f.post.drift != NB_DRIFT_NONE) f.pos_rw[f.begin + i] = p;
+        if (f.acc_out) f.acc_out[i] = a;
+        if (f.stats) {   // src/SimulationStats.cu:29-60
+            const double vv = f.dim == 2 ? (double)sqrtf(v.x * v.x + v.y * v.y)
+                                         : sqrt((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+            lm = vv * (double)p.w;
+            lk = 0.5 * vv * vv * (double)p.w;
+        }
+    }
+    if (f.stats) {
+        for (int o = 16; o > 0; o >>= 1) {
+            lm += __shfl_xor_sync(0xffffffffu, lm, o);
+            lk += __shfl_xor_sync(0xffffffffu, lk, o);
+        }
+        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = lm; red[1][threadIdx.x >> 5] = lk; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double m = 0.0, k = 0.0;
+            for (int w = 0; w < 8; w++) { m += red[0][w]; k += red[1][w]; }
+            f.stats[2 * blockIdx.x] = m;
+            f.stats[2 * blockIdx.x + 1] = k;
+        }
+    }
+}
+
 // Per source tile: are all masses equal to the reference mass (the mass of body n/2)?  The last block to finish then
 // decides whether hoisting is safe at all: m_ref must be a normal positive number with a finite reciprocal, and the
 // largest |m_j| / m_ref (what a mixed tile carries instead of m_j) must stay finite in FP32.  Otherwise mref[2] = 0 and
@@ -235,8 +314,23 @@ __global__ void __launch_bounds__(256) classify_tiles_kernel(const float4* __res
                                                             unsigned char* __restrict__ tile_uniform,
                                                             float* __restrict__ mref,      // [0] m_ref, [1] 1/m_ref, [2] hoisting on
                                                             unsigned int* __restrict__ ticket,
-                                                            float* __restrict__ tile_max) {
+                                                            float* __restrict__ tile_max, const DirectFused fused) {
     __shared__ float red[8];
+    if (fused.pre.drift != NB_DRIFT_NONE) {   // the stepper's pre-force drift of this tile's bodies that lie in the slice
+        for (int j = threadIdx.x; j < TILE; j += blockDim.x) {
+            const int i = blockIdx.x * TILE + j - fused.begin;
+            if (i >= 0 && i < fused.count) {
+                float4 p = fused.pos_rw[fused.begin + i];
+                const float4 v = fused.vel[i];
+                p.x = drift1g(fused.pre, p.x, v.x, 0.f);
+                p.y = drift1g(fused.pre, p.y, v.y, 0.f);
+                p.z = drift1g(fused.pre, p.z, v.z, 0.f);
+                fused.pos_rw[fused.begin + i] = p;
+            }
+        }
+        __syncthreads();   // the mass of body n/2 and of this tile are read below; the drift leaves .w alone, but the
+                           // writes of this block must not race with its own reads of the same float4
+    }
     __shared__ bool last;
     const float m = pos[n / 2].w;
     const bool usable = m >= 1.0e-30f && m <= 1.0e30f;
@@ -303,8 +397,18 @@ int env_int(const char* name, int dflt) {
 
 }  // namespace
 
+static int direct_launch(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
+                         int dim, float softening, int flags, cudaStream_t stream, const DirectFused* fused, bool plan_only);
+
 int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
                      int dim, float softening, int flags, cudaStream_t stream) {
+    return direct_launch(ctx, pos, n, target_begin, target_count, acc, dim, softening, flags, stream, nullptr, false);
+}
+
+// plan_only: make every one-time preparation (kernel attributes, scratch reservations) and launch nothing, so that the
+// same call can afterwards run inside a stream capture
+static int direct_launch(nb_context* ctx, const float* pos, int n, int target_begin, int target_count, float* acc,
+                         int dim, float softening, int flags, cudaStream_t stream, const DirectFused* fused, bool plan_only) {
     if (!ctx) return NB_ERR_INVALID;
     if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
     if (!nb_softening_ok(softening)) return nb_fail(ctx, NB_ERR_INVALID, "softening must be >= 0");
@@ -312,7 +416,7 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     if (n < 0 || target_begin < 0 || target_count < 0 || (long long)target_begin + target_count > n)
         return nb_fail(ctx, NB_ERR_INVALID, "target slice outside [0, n)");
     if (target_count == 0) return NB_OK;
-    if (!pos || !acc) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
+    if (!pos || (!acc && !fused)) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
 
     const int ntiles = (n + TILE - 1) / TILE;
@@ -364,7 +468,7 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     if (jsplit < 1) jsplit = 1;
 
     float4* out = reinterpret_cast<float4*>(acc);
-    if (jsplit > 1) {
+    if (jsplit > 1 || fused) {   // the fused step always goes through the scratch: its last kernel is the one that moves bodies
         rc = nb_reserve(ctx, &ctx->partial, &ctx->partial_bytes, (size_t)jsplit * target_count * sizeof(float4));
         if (rc) return rc;
         out = reinterpret_cast<float4*>(ctx->partial);
@@ -382,16 +486,27 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
         if (ctx->tile_flags_bytes != had) NB_CUDA(ctx, cudaMemset(ctx->tile_flags, 0, 64));   // the ticket starts at 0
         mref_d = reinterpret_cast<float*>(ctx->tile_flags);
         flags_d = reinterpret_cast<unsigned char*>(ctx->tile_flags) + 64;
-        classify_tiles_kernel<<<ntiles, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, flags_d, mref_d,
-                                                          reinterpret_cast<unsigned int*>(ctx->tile_flags) + 4,
-                                                          reinterpret_cast<float*>(flags_d + flag_bytes));
+        if (!plan_only) {
+            DirectFused none{};
+            classify_tiles_kernel<<<ntiles, 256, 0, stream>>>(reinterpret_cast<const float4*>(pos), n, flags_d, mref_d,
+                                                              reinterpret_cast<unsigned int*>(ctx->tile_flags) + 4,
+                                                              reinterpret_cast<float*>(flags_d + flag_bytes), fused ? *fused : none);
+        }
+        launches++;
+    } else if (fused && fused->pre.drift != NB_DRIFT_NONE) {
+        if (!plan_only) pre_drift_kernel<<<(fused->count + 255) / 256, 256, 0, stream>>>(*fused);
         launches++;
     }
+    if (plan_only) return NB_OK;
     dim3 grid(tblocks, jsplit);
     const int two_level = (flags & NB_DIRECT_ORDERED) ? 0 : 1;
     v.fn<<<grid, NT, smem_bytes(v.pairs), stream>>>(reinterpret_cast<const float4*>(pos), n, target_begin, target_count,
                                                     softening, out, jsplit, flags_d, mref_d, two_level);
-    if (jsplit > 1) {
+    if (fused) {
+        reduce_step_kernel<<<(target_count + 255) / 256, 256, 0, stream>>>(reinterpret_cast<const float4*>(ctx->partial), jsplit,
+                                                                          *fused);
+        launches++;
+    } else if (jsplit > 1) {
         reduce_partials_kernel<<<(target_count + 255) / 256, 256, 0, stream>>>(
             reinterpret_cast<const float4*>(ctx->partial), target_count, jsplit, reinterpret_cast<float4*>(acc));
         launches++;
@@ -400,6 +515,65 @@ int nb_direct_launch(nb_context* ctx, const float* pos, int n, int target_begin,
     ctx->last_jsplit = jsplit;
     ctx->last_blocks = tblocks * jsplit;
     ctx->last_launches = launches;
+    return NB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// nb_direct_step_slice -- one [pre-force drift; force; kick; drift] group of a stepper on a target slice, 3 launches
+// instead of 5 (include/nbody_b200.h).  Small systems are launch-bound: the launches are captured once into a CUDA graph
+// and replayed while the call's arguments stay the same.
+// ------------------------------------------------------------------------------------------------------
+extern "C" int nb_direct_step_slice(nb_context* ctx, float* pos, float* vel, int n, const nb_direct_step* step, void* stream_) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (!step) return nb_fail(ctx, NB_ERR_INVALID, "step description is NULL");
+    auto drift_ok = [](int k) { return k >= NB_DRIFT_NONE && k <= NB_DRIFT_VDT_F64; };   // NB_DRIFT_VV_F64 needs the old acceleration
+    auto kick_ok = [](int k) { return k >= NB_KICK_NONE && k <= NB_KICK_DTA_F64; };      // NB_KICK_MEAN_F64 needs two
+    if (!drift_ok(step->pre_drift_kind) || !drift_ok(step->drift_kind) || !kick_ok(step->kick_kind))
+        return nb_fail(ctx, NB_ERR_INVALID, "kick/drift kind not available in the fused step");
+    if (step->target_count > 0 && !vel) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    DirectFused f{};
+    f.pos_rw = reinterpret_cast<float4*>(pos);
+    f.vel = reinterpret_cast<float4*>(vel);
+    f.begin = step->target_begin;
+    f.count = step->target_count;
+    f.pre = SubstepArgs{NB_KICK_NONE, step->pre_drift_kind, step->dt, 0.0, step->pre_drift_coef};
+    f.post = SubstepArgs{step->kick_kind, step->drift_kind, step->dt, step->kick_coef, step->drift_coef};
+    f.acc_out = reinterpret_cast<float4*>(step->acc_out);
+    f.stats = step->stats_out;
+    f.dim = step->dim;
+    static const int graph_max_n = env_int("NB_DIRECT_GRAPH_MAX_N", 65536);
+    if (n > graph_max_n || step->target_count == 0)
+        return direct_launch(ctx, pos, n, step->target_begin, step->target_count, nullptr, step->dim, step->softening, step->flags,
+                             stream, &f, false);
+    // launch-bound sizes: replay a captured graph of the same call
+    struct Key { const float* pos; const float* vel; int n; nb_direct_step st; } key;
+    std::memset(&key, 0, sizeof(key));
+    key.pos = pos; key.vel = vel; key.n = n; key.st = *step;
+    static_assert(sizeof(Key) <= sizeof(ctx->direct_graph_key), "graph key storage");
+    if (!ctx->direct_graph || std::memcmp(&key, ctx->direct_graph_key, sizeof(key)) != 0) {
+        int rc = direct_launch(ctx, pos, n, step->target_begin, step->target_count, nullptr, step->dim, step->softening,
+                               step->flags, stream, &f, true);   // attributes + scratch: not inside the capture
+        if (rc) return rc;
+        if (ctx->direct_graph) { cudaGraphExecDestroy((cudaGraphExec_t)ctx->direct_graph); ctx->direct_graph = nullptr; }
+        if (!ctx->direct_capture_stream)
+            NB_CUDA(ctx, cudaStreamCreateWithFlags((cudaStream_t*)&ctx->direct_capture_stream, cudaStreamNonBlocking));
+        cudaStream_t cs = (cudaStream_t)ctx->direct_capture_stream;
+        NB_CUDA(ctx, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+        rc = direct_launch(ctx, pos, n, step->target_begin, step->target_count, nullptr, step->dim, step->softening, step->flags,
+                           cs, &f, false);
+        cudaGraph_t graph = nullptr;
+        cudaError_t e = cudaStreamEndCapture(cs, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) return nb_fail(ctx, NB_ERR_CUDA, "cudaStreamEndCapture", e);
+        cudaGraphExec_t exec = nullptr;
+        e = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) return nb_fail(ctx, NB_ERR_CUDA, "cudaGraphInstantiate", e);
+        ctx->direct_graph = exec;
+        std::memcpy(ctx->direct_graph_key, &key, sizeof(key));
+    }
+    NB_CUDA(ctx, cudaGraphLaunch((cudaGraphExec_t)ctx->direct_graph, stream));
     return NB_OK;
 }
 

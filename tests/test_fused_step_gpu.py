@@ -116,3 +116,58 @@ def test_fused_step_rejects_what_it_cannot_do(engine, pkg):
     fresh.close()
     with pytest.raises(ValueError):
         I.stepper_program("Velocity_Verlet", 1e-3)
+
+
+# ---- the direct sum: nb_direct_step_slice -------------------------------------------------------------------------------
+
+def _classic_direct(pkg, engine, name, pos, vel, dim, dt, steps, flags):
+    sysm = pkg.integrators.ShardedSystem(engine, pos.clone(), vel.clone(), "direct", dim, EPS, direct_flags=flags)
+    integ = getattr(pkg.IntegrationMethods, name)()
+    integ.setSystem(sysm)
+    for _ in range(steps):
+        integ.integrate(dt)
+    return sysm.pos, sysm.vel
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("n,dim,ordered", [(4096, 2, False), (5000, 3, True), (100000, 3, False)])
+def test_fused_direct_equals_separate_kernels(engine, pkg, name, n, dim, ordered):
+    """Kick and drift fused into the tile-classification and partial-sum kernels of the direct sum: the trajectory equals the
+    separate kernels' bit for bit -- below 65,536 bodies through the replayed CUDA graph, above it through plain launches,
+    in the default (split, hoisted) mode and in NB_DIRECT_ORDERED."""
+    import torch
+    steps, dt = 3, 1.0e-3
+    pos, vel = _state(pkg, n, 23, vz=(dim == 3))
+    flags = pkg.NB_DIRECT_ORDERED if ordered else pkg.NB_DIRECT_AUTO
+    want_p, want_v = _classic_direct(pkg, engine, name, pos, vel, dim, dt, steps, flags)
+    p, v = pos.clone(), vel.clone()
+    fused = pkg.integrators.FusedDirect(pkg.Engine(0, n), p, v, name, dim, EPS, flags=flags)
+    for _ in range(steps):
+        fused.step(dt)
+    torch.cuda.synchronize()
+    assert torch.equal(p, want_p) and torch.equal(v, want_v)
+
+
+def test_fused_direct_slices_and_stats(engine, pkg):
+    """Two slices of one system stepped by two FusedDirect objects (the sharded decomposition, with the all-gather a no-op
+    because both work on the same array) reproduce the one-slice trajectory, and the per-block sums of the epilogue are
+    SimulationStats' moment and kinetic energy."""
+    import torch
+    n, dt = 6000, 1.0e-3
+    pos, vel = _state(pkg, n, 29)
+    want_p, want_v = _classic_direct(pkg, engine, "Verlet_DKD", pos, vel, 2, dt, 1, pkg.NB_DIRECT_AUTO)
+    whole = pkg.integrators.FusedDirect(pkg.Engine(0, n), pos.clone(), vel.clone(), "Verlet_DKD", 2, EPS, stats=True)
+    m, k = whole.step(dt, stats=True)
+    torch.cuda.synchronize()
+    assert torch.equal(whole.pos, want_p) and torch.equal(whole.vel, want_v)
+    want = engine.stats(whole.pos, whole.vel, 2)
+    assert abs(m - want[0]) <= 1e-12 * abs(want[0]) and abs(k - want[1]) <= 1e-12 * abs(want[1]), (m, k, want)
+    # a slice alone: drift first (own kernel), then the fused force + kick + drift on [a, b)
+    a, b = 1000, 4321
+    p2, v2 = pos.clone(), vel.clone()
+    I = pkg.integrators
+    engine.integrate_substep(p2, v2, v2, 0, n, dt, 0, 0.0, I.DRIFT_HALF_F64, 0.0)
+    vs = v2[a:b].contiguous()
+    engine.direct_step_slice(p2, vs, 2, EPS, dt, a, b - a, kick=(I.KICK_F32, 0.0), drift=(I.DRIFT_HALF_F64, 0.0))
+    torch.cuda.synchronize()
+    assert torch.equal(p2[a:b], want_p[a:b]) and torch.equal(vs, want_v[a:b])
