@@ -326,6 +326,15 @@ int nb_ic_uniform_box(nb_context* ctx, float* pos, float* vel, int offset, int c
 int nb_ic_disk_velocities(nb_context* ctx, const float* pos, const float* acc, float* vel, int begin, int count, float cx, float cy,
                           int dim, float bulk_vx, float bulk_vy, void* stream);
 
+/* Standard (src/InitialConditions.cu:13-76, the reference's debug generator) with the counter-based generator: bodies
+ * [offset, offset+count) at centre + r (cos theta, sin theta), theta ~ U[0, 2 pi), r = (Exp(12) + 0.02) * 50000,
+ * z = sin(r/2000) * 2000, mass 100; body `offset` is the central mass 10^6.  nb_ic_standard_velocities is its second half
+ * (:49-73) after one force evaluation: v = sqrt(|F| dist) along rotation * (sin theta, -cos theta), body `offset` at rest;
+ * acc and vel are slice-local float4[count]. */
+int nb_ic_standard(nb_context* ctx, float* pos, int offset, int count, uint64_t seed, double cx, double cy, void* stream);
+int nb_ic_standard_velocities(nb_context* ctx, const float* pos, const float* acc, float* vel, int offset, int count,
+                              uint64_t seed, float rotation, void* stream);
+
 /* ---- calibration --------------------------------------------------------------------------------- */
 
 /* Measures this GPU's FP32 roofline denominators with register-resident microbenchmarks:

@@ -27,7 +27,7 @@ ABI_SYMBOLS = [
     "nb_direct_last_launch", "nb_direct_step_slice",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
     "nb_bh_last_counters", "nb_bh_build_info", "nb_bh_step_groups", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
-    "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities",
+    "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities", "nb_ic_standard", "nb_ic_standard_velocities",
     "nb_bh3d_accel", "nb_bh3d_accel_groups", "nb_bh3d_stages_host", "nb_bh3d_export_tree", "nb_bh3d_last_counters",
 ]
 
@@ -100,6 +100,8 @@ def lib():
         L.nb_ic_uniform_ellipsoid.argtypes = [vp, vp, vp, i, i, C.c_uint64, d, d, d, d, d, f, f, f, f, vp]
         L.nb_ic_uniform_box.argtypes = [vp, vp, vp, i, i, C.c_uint64, d, d, d, d, i, d, d, d, d, f, f, vp]
         L.nb_ic_disk_velocities.argtypes = [vp, vp, vp, vp, i, i, f, f, i, f, f, vp]
+        L.nb_ic_standard.argtypes = [vp, vp, i, i, C.c_uint64, d, d, vp]
+        L.nb_ic_standard_velocities.argtypes = [vp, vp, vp, vp, i, i, C.c_uint64, f, vp]
         L.nb_stats.argtypes = [vp, vp, vp, i, i, i, i, C.POINTER(C.c_double), vp]
         L.nb_integrate_substep.argtypes = [vp, vp, vp, vp, vp, i, i, f, i, C.c_double, i, C.c_double, vp]
         _lib = L
@@ -303,6 +305,15 @@ class Engine:
         self._check(lib().nb_ic_disk_velocities(self._h, pos.data_ptr(), acc.data_ptr(), vel.data_ptr(), begin, count,
                                                 centre[0], centre[1], dim, bulk_velocity[0], bulk_velocity[1],
                                                 _stream_ptr(stream)), "nb_ic_disk_velocities")
+
+    def ic_standard(self, pos, offset, count, seed=1, centre=(0.0, 0.0), stream=None):
+        """Standard (src/InitialConditions.cu:13-47) written straight into device memory."""
+        self._check(lib().nb_ic_standard(self._h, pos.data_ptr(), offset, count, seed, centre[0], centre[1], _stream_ptr(stream)),
+                    "nb_ic_standard")
+
+    def ic_standard_velocities(self, pos, acc, vel, offset, count, seed=1, rotation=1.0, stream=None):
+        self._check(lib().nb_ic_standard_velocities(self._h, pos.data_ptr(), acc.data_ptr(), vel.data_ptr(), offset, count, seed,
+                                                    rotation, _stream_ptr(stream)), "nb_ic_standard_velocities")
 
     # -- Barnes-Hut in 3D (octree; no reference counterpart) --------------------------------------------------
     def bh3d_accel(self, pos, acc, theta, softening, flags=0, stream=None):

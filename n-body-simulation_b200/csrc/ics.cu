@@ -83,9 +83,67 @@ __global__ void disk_velocity_kernel(const float4* __restrict__ pos, const float
     vel[i] = make_float4(__fadd_rn(-vy, bvx), __fadd_rn(vx, bvy), vz, 0.f);
 }
 
+// Standard (src/InitialConditions.cu:13-76, the reference's "debug version"): theta ~ U[0, 2 pi), r = (Exp(12) + 0.02) * 50000,
+// pos = centre + r (cos theta, sin theta), z = sin(r / 2000) * 2000 (FP32, :42), mass 100; body `offset` is the central mass
+// 10^6 at the centre.  Velocities after one force evaluation (:49-73): v = sqrt(|F| dist), dist to the central body with the
+// 0.0001 softening, direction rotation * (sin theta, -cos theta) with theta from the same generator.
+__global__ void standard_kernel(float4* __restrict__ pos, int offset, int count, unsigned long long seed, double cx, double cy) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const float theta = (float)(uniform01(seed, 0, i) * 6.283185307179586);
+    const float r = (float)((-log(1.0 - uniform01(seed, 1, i)) / 12.0 + 0.02) * 50000.0);
+    float4 p;
+    p.x = (float)(cx + (double)r * cos((double)theta));
+    p.y = (float)(cy + (double)r * sin((double)theta));
+    p.z = __fmul_rn(sinf(__fdiv_rn(r, 2000.f)), 2000.f);
+    p.w = 100.f;
+    if (i == 0) p = make_float4((float)cx, (float)cy, 0.f, 1000000.f);
+    pos[offset + i] = p;
+}
+
+__global__ void standard_velocity_kernel(const float4* __restrict__ pos, const float4* __restrict__ acc, float4* __restrict__ vel,
+                                         int offset, int count, unsigned long long seed, float rotation) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const float4 c = pos[offset], p = pos[offset + i], a = acc[i];
+    const float dx = __fsub_rn(c.x, p.x), dy = __fsub_rn(c.y, p.y), dz = __fsub_rn(c.z, p.z);
+    const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)), 0.0001f));
+    const float F = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(a.x, a.x), __fmul_rn(a.y, a.y)), __fmul_rn(a.z, a.z)));
+    const float v = __fsqrt_rn(__fmul_rn(dist, F));
+    const double theta = (double)(float)(uniform01(seed, 0, i) * 6.283185307179586);
+    float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i != 0) {
+        w.x = __fmul_rn(__fmul_rn(rotation, v), (float)sin(theta));
+        w.y = __fmul_rn(__fmul_rn(-rotation, v), (float)cos(theta));
+    }
+    vel[i] = w;
+}
+
 }  // namespace
 
 extern "C" {
+
+int nb_ic_standard(nb_context* ctx, float* pos, int offset, int count, uint64_t seed, double cx, double cy, void* stream) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
+    if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    standard_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, offset, count, seed, cx, cy);
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
+
+int nb_ic_standard_velocities(nb_context* ctx, const float* pos, const float* acc, float* vel, int offset, int count, uint64_t seed,
+                              float rotation, void* stream) {
+    if (!ctx) return NB_ERR_INVALID;
+    if (offset < 0 || count < 0 || (count > 0 && (!pos || !acc || !vel))) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
+    if (count == 0) return NB_OK;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    standard_velocity_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const float4*)pos, (const float4*)acc,
+                                                                                   (float4*)vel, offset, count, seed, rotation);
+    NB_CUDA(ctx, cudaGetLastError());
+    return NB_OK;
+}
 
 int nb_ic_uniform_ellipsoid(nb_context* ctx, float* pos, float* vel, int offset, int count, uint64_t seed, double cx, double cy,
                             double rx, double ry, double z_half_height, float mass, float central_mass, float vx, float vy,

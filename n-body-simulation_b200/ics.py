@@ -128,3 +128,34 @@ def cold_collapse_late(n, seed=2, radius=30000.0, mass=70000.0, clumps=12):
     pos[:, 1] = np.where(in_clump, (cy[which] + rr * np.sin(2 * np.pi * u2)), disc[:, 1]).astype(np.float32)
     pos[:, 3] = np.float32(mass)
     return pos
+
+
+def standard(n, seed=1, centre=(0.0, 0.0)):
+    """Standard (src/InitialConditions.cu:13-47, the reference's debug generator): theta ~ U[0, 2 pi),
+    r = (Exp(12) + 0.02) * 50000, z = sin(r / 2000) * 2000, mass 100, body 0 = the central mass 10^6.
+    Returns (pos float32 [n,4], theta float32 [n]); theta feeds standard_velocities."""
+    theta = (uniform01(seed, 0, n) * 6.283185307179586).astype(np.float32)
+    r = ((-np.log(1.0 - uniform01(seed, 1, n)) / 12.0 + 0.02) * 50000.0).astype(np.float32)
+    pos = np.zeros((n, 4), np.float32)
+    pos[:, 0] = (centre[0] + r.astype(np.float64) * np.cos(theta.astype(np.float64))).astype(np.float32)
+    pos[:, 1] = (centre[1] + r.astype(np.float64) * np.sin(theta.astype(np.float64))).astype(np.float32)
+    pos[:, 2] = np.sin(r / np.float32(2000.0), dtype=np.float32) * np.float32(2000.0)
+    pos[:, 3] = np.float32(100.0)
+    if n > 0:
+        pos[0] = (centre[0], centre[1], 0.0, 1000000.0)
+    return pos, theta
+
+
+def standard_velocities(pos, acc, theta, rotation=1.0):
+    """The velocity loop of Standard::initialize (src/InitialConditions.cu:49-73): v = sqrt(|F| dist) along
+    rotation * (sin theta, -cos theta); the central body stays at rest."""
+    d = pos[0, :3] - pos[:, :3]
+    dist = np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2] + np.float32(0.0001), dtype=np.float32)
+    F = np.sqrt(acc[:, 0] * acc[:, 0] + acc[:, 1] * acc[:, 1] + acc[:, 2] * acc[:, 2], dtype=np.float32)
+    v = np.sqrt(dist * F, dtype=np.float32)
+    vel = np.zeros((pos.shape[0], 4), np.float32)
+    rot = np.float32(rotation)
+    vel[:, 0] = (rot * v) * np.sin(theta.astype(np.float64)).astype(np.float32)
+    vel[:, 1] = (-rot * v) * np.cos(theta.astype(np.float64)).astype(np.float32)
+    vel[0] = 0
+    return vel

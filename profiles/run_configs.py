@@ -36,16 +36,25 @@ def timed_steps(fn, steps, warmup=3):
     return (time.perf_counter() - t0) / steps
 
 
-def ours(n, pos_h, method, integ_name, dim, theta, steps):
+def ours(n, pos_h, method, integ_name, dim, theta, steps, fused=True):
+    """fused: the kick / drift kernels of the stepper ride on the force kernels (nb_direct_step_slice, nb_bh_step_groups);
+    else the separate kernels of round 1 (ShardedSystem + the mirrored IntegrationMethods classes)."""
     eng = pkg.Engine(0, n)
     pos = torch.from_numpy(pos_h).cuda()
     vel = torch.zeros(n, 4, device="cuda")
-    s = pkg.integrators.ShardedSystem(eng, pos, vel, method, dim, EPS, theta)
-    integ = getattr(pkg.IntegrationMethods, integ_name)()
-    integ.setSystem(s)
-    dt = timed_steps(lambda: integ.integrate(DT), steps)
+    if fused:
+        s = (pkg.integrators.FusedDirect(eng, pos, vel, integ_name, dim, EPS) if method == "direct"
+             else pkg.integrators.FusedBarnesHut(eng, pos, vel, integ_name, theta, EPS))
+        dt = timed_steps(lambda: s.step(DT), steps)
+        evals = len(pkg.integrators.stepper_program(integ_name, DT)[1])
+    else:
+        s = pkg.integrators.ShardedSystem(eng, pos, vel, method, dim, EPS, theta)
+        integ = getattr(pkg.IntegrationMethods, integ_name)()
+        integ.setSystem(s)
+        dt = timed_steps(lambda: integ.integrate(DT), steps)
+        evals = integ.force_evaluations
     eng.close()
-    return dt, integ.force_evaluations
+    return dt, evals
 
 
 def reference_force(n, pos_h, method, dim, theta, reps):
@@ -75,16 +84,20 @@ configs = [
     ("1 direct N=16384 uniform disk, Leapfrog", 16384, "disk", "direct", "Verlet_DKD", 2, 0.5, 100),
     ("2 direct N=1048576, Leapfrog (1 GPU)", 1 << 20, "disk", "direct", "Verlet_DKD", 2, 0.5, 3),
     ("3 Barnes-Hut N=1048576 theta=0.5, Leapfrog", 1 << 20, "disk", "bh", "Verlet_DKD", 2, 0.5, 20),
-    ("4 Barnes-Hut cold collapse N=1048576 theta=0.5, PEFRL", 1 << 20, "disk", "bh", "PEFRL", 2, 0.5, 10),
+    ("4 Barnes-Hut cold collapse N=1048576 theta=0.5, PEFRL (late state: knots over a diffuse disc, at rest)", 1 << 20, "collapse", "bh", "PEFRL", 2, 0.5, 10),
     ("5 Barnes-Hut two-galaxy N=16777216 theta=0.7, Forest-Ruth (1 GPU)", 1 << 24, "merger", "bh", "ForestRuth", 2, 0.7, 3),
 ]
 only = sys.argv[1:] if len(sys.argv) > 1 else None
 for name, n, ic, method, integ, dim, theta, steps in configs:
     if only and name[0] not in only:
         continue
-    pos_h = pkg.ics.uniform_disk(n, seed=1) if ic == "disk" else pkg.ics.two_galaxies(n)
+    pos_h = {"disk": lambda: pkg.ics.uniform_disk(n, seed=1), "merger": lambda: pkg.ics.two_galaxies(n),
+             "collapse": lambda: pkg.ics.cold_collapse_late(n, seed=2)}[ic]()
     dt, evals = ours(n, pos_h, method, integ, dim, theta, steps)
     line = {"config": name, "ours_ms_per_step": dt * 1e3, "ours_steps_per_s": 1 / dt, "force_evaluations_per_step": evals}
+    if n <= (1 << 20):
+        dts, _ = ours(n, pos_h, method, integ, dim, theta, steps, fused=False)
+        line["ours_ms_per_step_separate_kernels"] = dts * 1e3
     if method == "direct":
         line["ours_interactions_per_s"] = evals * float(n) * n / dt
     r = reference_force(n, pos_h, method, dim, theta, 2 if n >= (1 << 20) else 10)

@@ -161,7 +161,7 @@ def test_fused_direct_slices_and_stats(engine, pkg):
     torch.cuda.synchronize()
     assert torch.equal(whole.pos, want_p) and torch.equal(whole.vel, want_v)
     want = engine.stats(whole.pos, whole.vel, 2)
-    assert abs(m - want[0]) <= 1e-12 * abs(want[0]) and abs(k - want[1]) <= 1e-12 * abs(want[1]), (m, k, want)
+    assert abs(m - want[0]) <= 1e-11 * abs(want[0]) and abs(k - want[1]) <= 1e-11 * abs(want[1]), (m, k, want)   # FP64 sums, other order
     # a slice alone: drift first (own kernel), then the fused force + kick + drift on [a, b)
     a, b = 1000, 4321
     p2, v2 = pos.clone(), vel.clone()

@@ -206,3 +206,30 @@ def test_device_uniform_box_matches_the_host_generator(engine, pkg):
     engine.ic_uniform_box(pos, 0, 0)
     with pytest.raises(RuntimeError):
         engine.ic_uniform_box(pos, 0, 10, dim=4)
+
+
+def test_device_standard_generator_matches_the_host_twin(engine, pkg):
+    """nb_ic_standard / nb_ic_standard_velocities (InitialConditions::Standard, src/InitialConditions.cu:13-76) against
+    ics.standard / ics.standard_velocities: masses and the central body bit for bit, positions and velocities within one
+    FP32 ulp (double cos / sin / log and FP32 sin of the device against the host's)."""
+    import torch
+    n = 100000
+    host, theta = pkg.ics.standard(n, seed=9, centre=(100.0, -50.0))
+    pos = torch.zeros(n + 3, 4, device="cuda")
+    engine.ic_standard(pos, 3, n, seed=9, centre=(100.0, -50.0))
+    torch.cuda.synchronize()
+    dev = pos.cpu().numpy()
+    assert np.all(dev[:3] == 0) and np.array_equal(dev[3:, 3], host[:, 3]) and np.array_equal(dev[3], host[0])
+    ulp = np.spacing(np.maximum(np.abs(host[:, :3]), 1.0).astype(np.float32))
+    assert np.all(np.abs(dev[3:, :3] - host[:, :3]) <= 2 * ulp) and np.mean(dev[3:, :2] == host[:, :2]) > 0.99
+    # velocities from a force evaluation on the HOST positions (so that both sides see the same accelerations)
+    dpos = torch.from_numpy(host).cuda()
+    acc = torch.zeros(n, 4, device="cuda")
+    engine.direct_accel(dpos, acc, 3, EPS)
+    vel = torch.zeros(n, 4, device="cuda")
+    engine.ic_standard_velocities(dpos, acc, vel, 0, n, seed=9, rotation=-1.0)
+    torch.cuda.synchronize()
+    want = pkg.ics.standard_velocities(host, acc.cpu().numpy(), theta, rotation=-1.0)
+    got = vel.cpu().numpy()
+    ulp = np.spacing(np.maximum(np.abs(want), 1e-3).astype(np.float32))
+    assert np.all(got[0] == 0) and np.all(np.abs(got - want) <= 2 * ulp), np.abs(got - want).max()
