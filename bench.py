@@ -406,12 +406,26 @@ def main():
             def bh_eval():
                 eng.bh_accel_groups(p2, a2, THETA, EPS, g0, g1 - g0)
             eval_ms = timed(bh_eval, ksteps, 3) / ksteps
+            # this rank's own build + walk time (timed() above returns the slowest rank's): the spread is the load imbalance
+            # of equal group counts per rank
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(ksteps):
+                bh_eval()
+            e1.record()
+            torch.cuda.synchronize()
+            own = torch.tensor([e0.elapsed_time(e1) / ksteps], device=dev, dtype=torch.float64)
+            per_rank = [own.clone() for _ in range(world)]
+            if world > 1:
+                dist.all_gather(per_rank, own)
+            per_rank = [float(t.item()) for t in per_rank]
             bh = {"metric": "BH Leapfrog steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
                   "ms_per_step": bh_ms, "n": nb, "theta": THETA,
                   "step": "Verlet_DKD: drift (fused into the bounds kernel) + build + walk with kick/drift epilogue"
                           + (" + all-gather of 16 B/body rows (NCCL)" if world > 1 else ""),
                   "collective_ms_per_step": coll_ms, "collective_bytes_per_step": nb * 16 if world > 1 else 0,
-                  "force_evaluation_ms": eval_ms,
+                  "force_evaluation_ms": eval_ms, "force_evaluation_ms_per_rank_warm_l2": per_rank,
                   "force_evaluation_note": "nb_bh_accel_groups alone on this rank's groups (build + walk, no kick/drift, no collective)"}
             if rank == 0:
                 eng.bh_accel_groups(p2, a2, THETA, EPS, 0, groups, flags=pkg.NB_BH_COUNT_WALK)

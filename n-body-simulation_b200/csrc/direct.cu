@@ -425,7 +425,13 @@ static int direct_launch(nb_context* ctx, const float* pos, int n, int target_be
     // choose the register blocking: 2 * BIG targets/thread when there are enough targets to fill the GPU with
     // them, else 4 (finer granularity); NB_DIRECT_PAIRS (2 = small, 4 = big) overrides for tuning.
     int pairs = env_int("NB_DIRECT_PAIRS", 0);
-    if (pairs != 2 && pairs != 4) pairs = (target_count >= ctx->sm_count * 2 * NT * 2 * BIG) ? 4 : 2;
+    if (pairs != 2 && pairs != 4) {
+        // the big variant as soon as its target blocks times the admissible source-range splits fill two blocks per SM
+        // (a 1/8 slice of a million bodies on 8 GPUs qualifies; 16,384 bodies do not)
+        const long long big_blocks = (target_count + NT * 2 * BIG - 1) / (NT * 2 * BIG);
+        const int max_js = (flags & NB_DIRECT_ORDERED) ? 1 : (ntiles / 2 > 64 ? 64 : (ntiles / 2 < 1 ? 1 : ntiles / 2));
+        pairs = (big_blocks * max_js >= 2LL * ctx->sm_count) ? 4 : 2;
+    }
     // Hoisting the common mass out of the sum changes the rounding (not the order) of the sum: exact mode keeps
     // the reference arithmetic; NB_DIRECT_NO_HOIST switches it off for tuning.
     const bool hoist = !(flags & (NB_DIRECT_ORDERED | NB_DIRECT_NO_HOIST)) && env_int("NB_DIRECT_NO_HOIST", 0) == 0;
