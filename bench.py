@@ -312,7 +312,7 @@ def main():
     tiles = pos_h[: (n // 1024) * 1024, 3].reshape(-1, 1024)
     roofline["hoisted_tile_fraction"] = float((tiles == pos_h[n // 2, 3]).all(axis=1).sum()) / max((n + 1023) // 1024, 1)
     try:   # DRAM traffic of the dominant kernel from the committed ncu --set full capture (per launch)
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r02", "traffic.json")))
         if n == N_BODIES and dim == 3 and world == 1:
             roofline["traffic"] = tr["direct_kernel_n1048576"]["traffic_bytes"]
             roofline["traffic_source"] = tr["direct_kernel_n1048576"]["source"]

@@ -1045,7 +1045,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
             epi.rows[bi - epi.row_base] = make_float4(p.x, p.y, v.x, v.y);
         }
         if (epi.stats) {   // SimulationStats "moment" and kinetic energy of the kicked velocities (R2 formula, :34-36)
-            double vv = (double)sqrtf(v.x * v.x + v.y * v.y);
+            double vv = (double)sqrtf(__fmaf_rn(v.x, v.x, __fmul_rn(v.y, v.y)));
             double lm = valid ? vv * (double)p.w : 0.0, lk = valid ? 0.5 * vv * vv * (double)p.w : 0.0;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
@@ -1092,7 +1092,7 @@ __global__ void lone_body_kernel(const float4* __restrict__ pos, float4* __restr
         epi.rows[0 - epi.row_base] = make_float4(p.x, p.y, v.x, v.y);
     }
     if (epi.stats) {
-        const double vv = (double)sqrtf(v.x * v.x + v.y * v.y);
+        const double vv = (double)sqrtf(__fmaf_rn(v.x, v.x, __fmul_rn(v.y, v.y)));
         epi.stats[0] = vv * (double)p.w;
         epi.stats[1] = 0.5 * vv * vv * (double)p.w;
     }

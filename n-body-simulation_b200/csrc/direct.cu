@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(256) reduce_step_kernel(const float4* __restri
         if (f.post.drift != NB_DRIFT_NONE) f.pos_rw[f.begin + i] = p;
         if (f.acc_out) f.acc_out[i] = a;
         if (f.stats) {   // src/SimulationStats.cu:29-60
-            const double vv = f.dim == 2 ? (double)sqrtf(v.x * v.x + v.y * v.y)
+            const double vv = f.dim == 2 ? (double)sqrtf(__fmaf_rn(v.x, v.x, __fmul_rn(v.y, v.y)))
                                          : sqrt((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
             lm = vv * (double)p.w;
             lk = 0.5 * vv * vv * (double)p.w;

@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(ST_THREADS) kinetic_kernel(const float4* __res
         const float4 w = vel[i];
         const double m = pos[target_begin + i].w;
         double v;
-        if (dim == 2) v = (double)sqrtf(w.x * w.x + w.y * w.y);   // :34 the argument is a float expression, so `sqrt` there is
+        if (dim == 2) v = (double)sqrtf(__fmaf_rn(w.x, w.x, __fmul_rn(w.y, w.y)));   // :34 the argument is a float expression (nvcc contracts it to fma(x, x, y*y)), so `sqrt` there is
                                                                    // the FP32 square root; only its result is promoted
         else v = sqrt((double)w.x * w.x + (double)w.y * w.y + (double)w.z * w.z);   // :51
         lm += v * m;
