@@ -385,10 +385,11 @@ def main():
             torch.cuda.synchronize()
             a2_init = a2.clone()
             v2 = torch.from_numpy(pkg.ics.disk_velocities(p2_h, a2.cpu().numpy())).to(dev)
-            stepper = pkg.integrators.FusedBarnesHut(eng, p2, v2, "Verlet_DKD", THETA, EPS, world, rank, dist)
+            p2p = world > 1 and os.environ.get("NB_BH_P2P", "1") != "0"
+            stepper = pkg.integrators.FusedBarnesHut(eng, p2, v2, "Verlet_DKD", THETA, EPS, world, rank, dist, p2p=p2p)
             coll_events = []
             if world > 1:
-                plain_gather = stepper._gather_rows
+                plain_gather = stepper._exchange
 
                 def timed_gather():
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -396,7 +397,7 @@ def main():
                     plain_gather()
                     e1.record()
                     coll_events.append((e0, e1))
-                stepper._gather_rows = timed_gather
+                stepper._exchange = timed_gather
             ksteps = max(args.steps, 10)
             bh_ms = timed(lambda: stepper.step(DT, lazy=True), ksteps, 3) / ksteps
             coll_ms = sum(e0.elapsed_time(e1) for e0, e1 in coll_events[-ksteps:]) / ksteps if coll_events else 0.0
@@ -423,7 +424,9 @@ def main():
             bh = {"metric": "BH Leapfrog steps/s (N=1M, theta=0.5)", "value": 1e3 / bh_ms, "unit": "steps/s",
                   "ms_per_step": bh_ms, "n": nb, "theta": THETA,
                   "step": "Verlet_DKD: drift (fused into the bounds kernel) + build + walk with kick/drift epilogue"
-                          + (" + all-gather of 16 B/body rows (NCCL)" if world > 1 else ""),
+                          + ((" + rows (16 B/body) stored into every rank's array by the walk epilogue over NVLink peer memory, "
+                              "one 4-byte all-reduce as barrier" if p2p else " + all-gather of 16 B/body rows (NCCL)") if world > 1 else ""),
+                  "exchange": ("peer stores in the walk epilogue + barrier" if p2p else "NCCL all-gather") if world > 1 else None,
                   "collective_ms_per_step": coll_ms, "collective_bytes_per_step": nb * 16 if world > 1 else 0,
                   "force_evaluation_ms": eval_ms, "force_evaluation_ms_per_rank_warm_l2": per_rank,
                   "force_evaluation_note": "nb_bh_accel_groups alone on this rank's groups (build + walk, no kick/drift, no collective)"}

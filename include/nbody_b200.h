@@ -251,6 +251,7 @@ int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, const float* a
  *   stats_out (device double[2 ceil(n/32)], may be NULL): per walked group g, [2g] = sum m|v| and [2g+1] = sum m v^2/2
  *       of the kicked velocities, lanes added in a fixed order -- the two sums of SimulationStats::computeStats
  *       (src/SimulationStats.cu:29-44) without a second pass over the bodies. */
+#define NB_MAX_PEERS 8
 typedef struct nb_bh_step {
     float theta, softening, dt;
     int flags;                 /* NB_BH_FRESH_BOUNDS / NB_BH_ACCUMULATE_BOUNDS */
@@ -267,6 +268,13 @@ typedef struct nb_bh_step {
     float* rows_out;           /* sharded: this rank's rows; NULL = update pos/vel in place */
     float* acc_out;            /* in-place mode only, may be NULL */
     double* stats_out;         /* may be NULL */
+    /* Sharded without a collective call: with n_rows_peers > 0 the epilogue stores each row into rows_peers[r][s] for
+     * every r -- s the GLOBAL sorted slot, each rows_peers[r] a float4[32 ceil(n/32)] array on rank r's GPU mapped into this
+     * process (nb_peer_open; this rank's own array is among them) -- so the all-gather happens inside the walk, as coalesced
+     * stores over NVLink.  rows_out is then ignored.  The caller double-buffers the arrays and separates consecutive
+     * force evaluations by one cross-rank barrier (integrators.FusedBarnesHut(p2p=True)). */
+    int n_rows_peers;
+    float* rows_peers[NB_MAX_PEERS];
 } nb_bh_step;
 int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_bh_step* step, void* stream);
 
@@ -293,6 +301,15 @@ typedef struct nb_direct_step {
     double* stats_out;
 } nb_direct_step;
 int nb_direct_step_slice(nb_context* ctx, float* pos, float* vel, int n, const nb_direct_step* step, void* stream);
+
+/* Device memory other processes of the same box can map (one process per GPU): nb_peer_alloc allocates `bytes` on the
+ * handle's device and fills `handle` (64 bytes, a CUDA IPC handle: send it to the other ranks by any means); nb_peer_open
+ * maps a buffer allocated by ANOTHER process into this one and returns a device pointer this GPU's kernels can store
+ * through (NVLink peer access).  nb_peer_close unmaps, nb_peer_free releases.  No counterpart in the single-GPU reference. */
+int nb_peer_alloc(nb_context* ctx, uint64_t bytes, void** ptr, unsigned char handle[64]);
+int nb_peer_open(nb_context* ctx, const unsigned char handle[64], void** ptr);
+int nb_peer_close(nb_context* ctx, void* ptr);
+int nb_peer_free(nb_context* ctx, void* ptr);
 
 /* ---- diagnostics (callers of the path) ------------------------------------- */
 

@@ -26,7 +26,8 @@ ABI_SYMBOLS = [
     "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_accel_noalloc",
     "nb_direct_last_launch", "nb_direct_step_slice",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
-    "nb_bh_last_counters", "nb_bh_build_info", "nb_bh_step_groups", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
+    "nb_bh_last_counters", "nb_bh_build_info", "nb_bh_step_groups", "nb_peer_alloc", "nb_peer_open", "nb_peer_close",
+    "nb_peer_free", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
     "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities", "nb_ic_standard", "nb_ic_standard_velocities",
     "nb_bh3d_accel", "nb_bh3d_accel_groups", "nb_bh3d_stages_host", "nb_bh3d_export_tree", "nb_bh3d_last_counters",
 ]
@@ -54,7 +55,31 @@ class BHStep(C.Structure):
                 ("kick_kind", C.c_int), ("kick_coef", C.c_double),
                 ("drift_kind", C.c_int), ("drift_coef", C.c_double),
                 ("rows_in", C.c_void_p), ("prev_drift_kind", C.c_int), ("prev_drift_coef", C.c_double),
-                ("rows_out", C.c_void_p), ("acc_out", C.c_void_p), ("stats_out", C.c_void_p)]
+                ("rows_out", C.c_void_p), ("acc_out", C.c_void_p), ("stats_out", C.c_void_p),
+                ("n_rows_peers", C.c_int), ("rows_peers", C.c_void_p * 8)]
+
+
+class PeerBuffer:
+    """Device memory other ranks can map (nb_peer_alloc / nb_peer_open).  `tensor` is a torch view of it (no copy)."""
+
+    def __init__(self, engine, shape, ptr, handle=None, opened=False):
+        self.engine, self.shape, self.ptr, self.handle, self.opened = engine, tuple(shape), ptr, handle, opened
+        n = 1
+        for d in self.shape:
+            n *= d
+        self.__cuda_array_interface__ = {"shape": self.shape, "typestr": "<f4", "data": (ptr, False), "version": 2,
+                                         "strides": None}
+        self.bytes = 4 * n
+
+    @property
+    def tensor(self):
+        import torch
+        return torch.as_tensor(self, device=torch.device("cuda", self.engine.device))
+
+    def release(self):
+        if self.ptr:
+            (lib().nb_peer_close if self.opened else lib().nb_peer_free)(self.engine._h, C.c_void_p(self.ptr))
+            self.ptr = 0
 
 
 def library_path():
@@ -88,6 +113,10 @@ def lib():
         L.nb_bh_last_counters.argtypes = [vp, C.POINTER(C.c_int64)]
         L.nb_bh_build_info.argtypes = [vp, C.POINTER(C.c_int64)]
         L.nb_bh_step_groups.argtypes = [vp, vp, vp, i, C.POINTER(BHStep), vp]
+        L.nb_peer_alloc.argtypes = [vp, C.c_uint64, C.POINTER(vp), C.c_char_p]
+        L.nb_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+        L.nb_peer_close.argtypes = [vp, vp]
+        L.nb_peer_free.argtypes = [vp, vp]
         L.nb_bh3d_accel.argtypes = [vp, vp, vp, i, f, f, i, vp]
         L.nb_bh3d_accel_groups.argtypes = [vp, vp, vp, i, f, f, i, i, i, vp]
         L.nb_bh3d_stages_host.argtypes = [vp, vp, i, vp, vp, vp]
@@ -240,7 +269,7 @@ class Engine:
 
     def bh_step_groups(self, pos, vel, theta, softening, dt, group_begin, group_count, pre_drift=(0, 0.0), kick=(0, 0.0),
                        drift=(0, 0.0), rows_in=None, prev_drift=(0, 0.0), rows_out=None, acc_out=None, stats_out=None,
-                       flags=NB_BH_FRESH_BOUNDS, stream=None):
+                       flags=NB_BH_FRESH_BOUNDS, stream=None, rows_peers=None):
         """One [pre-drift; force; kick; drift] group of a stepper with the kick and drift fused into the walk
         (nb_bh_step_groups).  pos, vel: CUDA float32 [n,4], updated in place unless rows_out is given."""
         n = pos.shape[0]
@@ -250,8 +279,26 @@ class Engine:
                     rows_out.data_ptr() if rows_out is not None else None,
                     acc_out.data_ptr() if acc_out is not None else None,
                     stats_out.data_ptr() if stats_out is not None else None)
+        if rows_peers:   # device pointers (ints) of every rank's rows array, this rank's own included
+            st.n_rows_peers = len(rows_peers)
+            for k, ptr in enumerate(rows_peers):
+                st.rows_peers[k] = ptr
         self._check(lib().nb_bh_step_groups(self._h, pos.data_ptr(), vel.data_ptr(), n, C.byref(st), _stream_ptr(stream)),
                     "nb_bh_step_groups")
+
+    def peer_alloc(self, shape):
+        """float32 device buffer of `shape` that other ranks can map; returns a PeerBuffer (handle = 64 bytes to send)."""
+        n = 1
+        for d in shape:
+            n *= d
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        self._check(lib().nb_peer_alloc(self._h, 4 * n, C.byref(ptr), handle), "nb_peer_alloc")
+        return PeerBuffer(self, shape, ptr.value, handle.raw)
+
+    def peer_open(self, handle, shape):
+        ptr = C.c_void_p()
+        self._check(lib().nb_peer_open(self._h, handle, C.byref(ptr)), "nb_peer_open")
+        return PeerBuffer(self, shape, ptr.value, handle, opened=True)
 
     def bh_build_info(self):
         c = (C.c_int64 * 4)()

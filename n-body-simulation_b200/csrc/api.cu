@@ -68,6 +68,45 @@ int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* 
     return NB_OK;
 }
 
+int nb_peer_alloc(nb_context* ctx, uint64_t bytes, void** ptr, unsigned char handle[64]) {
+    if (!ctx || !ptr || !handle || bytes == 0) return ctx ? nb_fail(ctx, NB_ERR_INVALID, "nb_peer_alloc: bad argument") : NB_ERR_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaMalloc(ptr, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, *ptr);
+    if (e != cudaSuccess) {
+        cudaFree(*ptr);
+        *ptr = nullptr;
+        return nb_fail(ctx, NB_ERR_CUDA, "cudaIpcGetMemHandle", e);
+    }
+    memcpy(handle, &h, 64);
+    return NB_OK;
+}
+
+int nb_peer_open(nb_context* ctx, const unsigned char handle[64], void** ptr) {
+    if (!ctx || !ptr || !handle) return ctx ? nb_fail(ctx, NB_ERR_INVALID, "nb_peer_open: bad argument") : NB_ERR_INVALID;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    NB_CUDA(ctx, cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return NB_OK;
+}
+
+int nb_peer_close(nb_context* ctx, void* ptr) {
+    if (!ctx) return NB_ERR_INVALID;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ptr) NB_CUDA(ctx, cudaIpcCloseMemHandle(ptr));
+    return NB_OK;
+}
+
+int nb_peer_free(nb_context* ctx, void* ptr) {
+    if (!ctx) return NB_ERR_INVALID;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ptr) NB_CUDA(ctx, cudaFree(ptr));
+    return NB_OK;
+}
+
 int nb_direct_accel(nb_context* ctx, const float* pos, float* acc, int n, int dim, float softening, int flags,
                     void* stream) {
     return nb_direct_launch(ctx, pos, n, 0, n, acc, dim, softening, flags, (cudaStream_t)stream);

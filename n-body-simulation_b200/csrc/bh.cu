@@ -140,6 +140,11 @@ struct WalkEpilogue {
     int row_base;
     SubstepArgs s;
     double* stats;
+    // mode 2 with n_peers > 0: the row goes straight into EVERY rank's rows array (float4[32 ceil(n/32)], indexed by the
+    // global sorted slot) -- plain coalesced stores to peer memory over NVLink, so the all-gather happens inside the
+    // walk instead of after it.  (Stores only; no bulk / TMA copy touches peer memory.)
+    int n_peers;
+    float4* rows_peer[NB_MAX_PEERS];
 };
 
 // ------------------------------------------------------------------------------------------------------
@@ -1042,7 +1047,14 @@ __global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const floa
             }
             if (acc && valid) acc[body] = make_float4(ax, ay, 0.f, 0.f);
         } else if (valid) {
-            epi.rows[bi - epi.row_base] = make_float4(p.x, p.y, v.x, v.y);
+            const float4 row = make_float4(p.x, p.y, v.x, v.y);
+            if (epi.n_peers > 0) {
+#pragma unroll
+                for (int r = 0; r < NB_MAX_PEERS; r++)     // constant indices: the pointers come straight from the parameter bank
+                    if (r < epi.n_peers) epi.rows_peer[r][bi] = row;
+            } else {
+                epi.rows[bi - epi.row_base] = row;
+            }
         }
         if (epi.stats) {   // SimulationStats "moment" and kinetic energy of the kicked velocities (R2 formula, :34-36)
             double vv = (double)sqrtf(__fmaf_rn(v.x, v.x, __fmul_rn(v.y, v.y)));
@@ -1088,6 +1100,10 @@ __global__ void lone_body_kernel(const float4* __restrict__ pos, float4* __restr
         epi.vel_rw[0] = v;
         epi.pos_rw[0] = p;
         if (acc) acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else if (epi.n_peers > 0) {
+#pragma unroll
+        for (int r = 0; r < NB_MAX_PEERS; r++)
+            if (r < epi.n_peers) epi.rows_peer[r][0] = make_float4(p.x, p.y, v.x, v.y);
     } else {
         epi.rows[0 - epi.row_base] = make_float4(p.x, p.y, v.x, v.y);
     }
@@ -1460,8 +1476,15 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     } else {
         prep.mode = step->pre_drift_kind != NB_DRIFT_NONE ? 1 : 0;
     }
+    if (step->n_rows_peers < 0 || step->n_rows_peers > NB_MAX_PEERS)
+        return nb_fail(ctx, NB_ERR_INVALID, "n_rows_peers outside [0, NB_MAX_PEERS]");
     WalkEpilogue epi{};
-    epi.mode = step->rows_out ? 2 : 1;
+    epi.mode = (step->rows_out || step->n_rows_peers > 0) ? 2 : 1;
+    epi.n_peers = step->n_rows_peers;
+    for (int r = 0; r < step->n_rows_peers; r++) {
+        if (!step->rows_peers[r]) return nb_fail(ctx, NB_ERR_INVALID, "rows_peers holds a NULL pointer");
+        epi.rows_peer[r] = reinterpret_cast<float4*>(step->rows_peers[r]);
+    }
     epi.pos_rw = reinterpret_cast<float4*>(pos);
     epi.vel_rw = reinterpret_cast<float4*>(vel);
     epi.rows = reinterpret_cast<float4*>(step->rows_out);

@@ -186,7 +186,10 @@ class FusedBarnesHut:
     `pos` / `vel` are current after materialize() (called by step() unless lazy=True)."""
 
     def __init__(self, engine, pos, vel, integrator="Verlet_DKD", theta=0.5, softening=1.01, world=1, rank=0, dist=None,
-                 flags=0, stats=False):
+                 flags=0, stats=False, p2p=False):
+        """p2p (sharded runs on one box): no all-gather call at all -- the walk's epilogue stores each row straight into
+        every rank's rows array over NVLink (the arrays are allocated by nb_peer_alloc and mapped by the other ranks);
+        two arrays alternate, and consecutive force evaluations are separated by one tiny all-reduce used as a barrier."""
         import torch
         from . import shard
         self.engine, self.pos, self.vel = engine, pos, vel
@@ -205,6 +208,25 @@ class FusedBarnesHut:
         self.stats_buf = torch.zeros(2 * self.groups, dtype=torch.float64, device=pos.device) if stats else None
         self.pending = None          # ((drift kind, coefficient), dt) of the evaluation whose rows are waiting in rows_all
         self.force_evaluations = 0
+        self.p2p = bool(p2p) and world > 1
+        if self.p2p:
+            shape = (32 * self.groups, 4)
+            self._mine = [engine.peer_alloc(shape) for _ in range(2)]
+            handles = [None] * world
+            dist.all_gather_object(handles, [b.handle for b in self._mine])
+            self._peers = [[self._mine[k] if r == rank else engine.peer_open(handles[r][k], shape) for r in range(world)]
+                           for k in range(2)]
+            self._rows = [b.tensor for b in self._mine]
+            self._flip = 0
+            self._token = torch.zeros(1, device=pos.device)
+            dist.all_reduce(self._token)      # everyone has mapped everyone before the first store
+
+    def _exchange(self):
+        """What follows a rank's walk: the all-gather of the rows, or (p2p) the barrier behind the peer stores."""
+        if self.p2p:
+            self.dist.all_reduce(self._token)
+        else:
+            self._gather_rows()
 
     def _gather_rows(self):
         if self.even:                # in place: every rank's rows already sit at their offset of rows_all
@@ -218,12 +240,24 @@ class FusedBarnesHut:
         e = self.engine
         sharded = self.world > 1
         rows_in, prev = (self.rows_all, self.pending[0]) if self.pending is not None else (None, (0, 0.0))
+        if self.p2p:
+            # rows of the previous evaluation sit in the array written then; this evaluation writes the other one
+            rows_in = self._rows[self._flip ^ 1] if self.pending is not None else None
+            e.bh_step_groups(self.pos, self.vel, self.theta, self.eps, dt, self.g0, self.g1 - self.g0, pre_drift=pre, kick=kick,
+                             drift=drift, rows_in=rows_in, prev_drift=prev, rows_peers=[b.ptr for b in self._peers[self._flip]],
+                             stats_out=self.stats_buf if stats else None, flags=self.flags)
+            self.force_evaluations += 1
+            self._exchange()                      # barrier: every rank's stores of this evaluation have landed
+            self.rows_all = self._rows[self._flip]
+            self._flip ^= 1
+            self.pending = (drift, dt)
+            return
         e.bh_step_groups(self.pos, self.vel, self.theta, self.eps, dt, self.g0, self.g1 - self.g0, pre_drift=pre, kick=kick,
                          drift=drift, rows_in=rows_in, prev_drift=prev, rows_out=self.rows_out if sharded else None,
                          stats_out=self.stats_buf if stats else None, flags=self.flags)
         self.force_evaluations += 1
         if sharded:
-            self._gather_rows()
+            self._exchange()
             self.pending = (drift, dt)
 
     def materialize(self):

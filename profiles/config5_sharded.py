@@ -21,6 +21,7 @@ if world > 1:
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 24
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 classic = len(sys.argv) > 3 and sys.argv[3] == "classic"
+p2p = len(sys.argv) > 3 and sys.argv[3] == "p2p"
 eng = pkg.Engine(local, n)
 pos = torch.from_numpy(pkg.ics.two_galaxies(n)).cuda()
 if classic:
@@ -32,7 +33,7 @@ if classic:
     step = lambda: integ.integrate(0.001)   # noqa: E731
 else:
     vel = torch.zeros(n, 4, device="cuda")
-    s = pkg.integrators.FusedBarnesHut(eng, pos, vel, "ForestRuth", 0.7, 1.01, world, rank, dist if world > 1 else None)
+    s = pkg.integrators.FusedBarnesHut(eng, pos, vel, "ForestRuth", 0.7, 1.01, world, rank, dist if world > 1 else None, p2p=p2p)
     step = lambda: s.step(0.001, lazy=True)   # noqa: E731
 step()
 torch.cuda.synchronize()
@@ -52,7 +53,7 @@ else:
 chk = pos[:, :2].double().sum().item()
 if rank == 0:
     print(json.dumps({"config": "5 Barnes-Hut two-galaxy N=%d theta=0.7 Forest-Ruth" % n, "n_gpus": world,
-                      "path": "classic" if classic else "fused", "ms_per_step": dt * 1e3,
+                      "path": "classic" if classic else ("fused, peer stores" if p2p else "fused, all-gather"), "ms_per_step": dt * 1e3,
                       "steps_per_s": 1 / dt, "position_checksum": chk}), flush=True)
 if world > 1:
     dist.destroy_process_group()

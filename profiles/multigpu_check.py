@@ -56,11 +56,14 @@ for n, name, steps in ((65536, "Verlet_DKD", 3), (100001, "PEFRL", 2), (50000, "
     one = pkg.integrators.FusedBarnesHut(pkg.Engine(local, n), p1, v1, name, 0.5, 1.01)
     pg, vg = torch.from_numpy(pos_h).cuda(), torch.from_numpy(vel_h).cuda()
     many = pkg.integrators.FusedBarnesHut(pkg.Engine(local, n), pg, vg, name, 0.5, 1.01, world, rank, dist, stats=True)
+    pp, vp = torch.from_numpy(pos_h).cuda(), torch.from_numpy(vel_h).cuda()
+    peer = pkg.integrators.FusedBarnesHut(pkg.Engine(local, n), pp, vp, name, 0.5, 1.01, world, rank, dist, p2p=True)
     for k in range(steps):
         one.step(1.0e-3)
         many.step(1.0e-3, lazy=(k + 1 < steps))
+        peer.step(1.0e-3, lazy=(k + 1 < steps))
     torch.cuda.synchronize()
-    same = bool(torch.equal(p1, pg) and torch.equal(v1, vg))
+    same = bool(torch.equal(p1, pg) and torch.equal(v1, vg) and torch.equal(p1, pp) and torch.equal(v1, vp))
     if not same and rank == 0:
         print("fused sharded trajectory differs:", n, name)
     ok &= same
