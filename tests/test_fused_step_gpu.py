@@ -171,3 +171,33 @@ def test_fused_direct_slices_and_stats(engine, pkg):
     engine.direct_step_slice(p2, vs, 2, EPS, dt, a, b - a, kick=(I.KICK_F32, 0.0), drift=(I.DRIFT_HALF_F64, 0.0))
     torch.cuda.synchronize()
     assert torch.equal(p2[a:b], want_p[a:b]) and torch.equal(vs, want_v[a:b])
+
+
+def test_rows_stored_through_peer_pointers_equal_rows_out(engine, pkg):
+    """The exchange inside the walk (n_rows_peers > 0): the epilogue stores each row into every array of a pointer list,
+    indexed by the global sorted slot.  On one GPU the 'peers' are three buffers of this process obtained from
+    nb_peer_alloc (on a multi-GPU box they are other ranks' buffers mapped with nb_peer_open, tests/test_multigpu_gpu.py):
+    each must hold exactly the rows the rows_out form produces, for a group range that starts inside the array."""
+    import torch
+    I = pkg.integrators
+    n, dt = 20000, 1.0e-3
+    pos, vel = _state(pkg, n, 31)
+    groups = (n + 31) // 32
+    g0, gc = 100, groups - 100
+    want = torch.full((32 * gc, 4), float("nan"), device="cuda")
+    engine.bh_step_groups(pos.clone(), vel.clone(), 0.5, EPS, dt, g0, gc, pre_drift=(I.DRIFT_HALF_F64, 0.0),
+                          kick=(I.KICK_F32, 0.0), drift=(I.DRIFT_HALF_F64, 0.0), rows_out=want)
+    bufs = [engine.peer_alloc((32 * groups, 4)) for _ in range(3)]
+    for b in bufs:
+        b.tensor.fill_(float("nan"))
+    engine.bh_step_groups(pos.clone(), vel.clone(), 0.5, EPS, dt, g0, gc, pre_drift=(I.DRIFT_HALF_F64, 0.0),
+                          kick=(I.KICK_F32, 0.0), drift=(I.DRIFT_HALF_F64, 0.0), rows_peers=[b.ptr for b in bufs])
+    torch.cuda.synchronize()
+    valid = n - 32 * g0
+    for b in bufs:
+        t = b.tensor
+        assert torch.equal(t[32 * g0:32 * g0 + valid], want[:valid])
+        assert torch.isnan(t[:32 * g0]).all()          # slots of groups this call did not walk stay untouched
+        b.release()
+    with pytest.raises(pkg.NbodyError):
+        engine.bh_step_groups(pos, vel, 0.5, EPS, dt, 0, 1, rows_peers=[0])
