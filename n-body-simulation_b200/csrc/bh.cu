@@ -1231,6 +1231,7 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
     nb_bh_state* st = ctx->bh;
     const float4* pos = reinterpret_cast<const float4*>(pos_);
     st->last_n = n;
+    if (upto >= 3) st->perm_valid = false;   // the sorts below overwrite the permutation a pending rows_in refers to
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
     int bblocks = std::min(1024, std::max(1, (n + 1023) / 1024));
     bounds_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, accumulate, st->counters + 4, prep);
@@ -1435,6 +1436,7 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     }
     st->last_n = n;
     st->bounds_valid = true;
+    st->perm_valid = false;
     NB_CUDA(ctx, cudaGraphLaunch(st->graph_exec, (cudaStream_t)stream));
     return NB_OK;
 }

@@ -36,6 +36,7 @@ struct nb_context {
     void* direct_graph = nullptr;            // cudaGraphExec_t
     void* direct_capture_stream = nullptr;   // cudaStream_t
     unsigned char direct_graph_key[160] = {0};
+    unsigned int scratch_epoch = 0;          // bumped whenever nb_reserve moves a scratch buffer: captured graphs hold the old address
 
     nb_bh_state* bh = nullptr;
     nb_bh3_state* bh3 = nullptr;
@@ -72,6 +73,7 @@ inline int nb_reserve(nb_context* ctx, void** ptr, size_t* have, size_t want) {
     if (*ptr) NB_CUDA(ctx, cudaFree(*ptr));
     *ptr = nullptr;
     *have = 0;
+    ctx->scratch_epoch++;
     NB_CUDA(ctx, cudaMalloc(ptr, want));
     *have = want;
     return NB_OK;

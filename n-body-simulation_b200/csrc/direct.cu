@@ -553,14 +553,15 @@ extern "C" int nb_direct_step_slice(nb_context* ctx, float* pos, float* vel, int
         return direct_launch(ctx, pos, n, step->target_begin, step->target_count, nullptr, step->dim, step->softening, step->flags,
                              stream, &f, false);
     // launch-bound sizes: replay a captured graph of the same call
-    struct Key { const float* pos; const float* vel; int n; nb_direct_step st; } key;
+    // attributes + scratch first, outside any capture; it may move a scratch buffer, which the key below then reflects
+    int rc = direct_launch(ctx, pos, n, step->target_begin, step->target_count, nullptr, step->dim, step->softening, step->flags,
+                           stream, &f, true);
+    if (rc) return rc;
+    struct Key { const float* pos; const float* vel; int n; unsigned int epoch; nb_direct_step st; } key;
     std::memset(&key, 0, sizeof(key));
-    key.pos = pos; key.vel = vel; key.n = n; key.st = *step;
+    key.pos = pos; key.vel = vel; key.n = n; key.epoch = ctx->scratch_epoch; key.st = *step;
     static_assert(sizeof(Key) <= sizeof(ctx->direct_graph_key), "graph key storage");
     if (!ctx->direct_graph || std::memcmp(&key, ctx->direct_graph_key, sizeof(key)) != 0) {
-        int rc = direct_launch(ctx, pos, n, step->target_begin, step->target_count, nullptr, step->dim, step->softening,
-                               step->flags, stream, &f, true);   // attributes + scratch: not inside the capture
-        if (rc) return rc;
         if (ctx->direct_graph) { cudaGraphExecDestroy((cudaGraphExec_t)ctx->direct_graph); ctx->direct_graph = nullptr; }
         if (!ctx->direct_capture_stream)
             NB_CUDA(ctx, cudaStreamCreateWithFlags((cudaStream_t*)&ctx->direct_capture_stream, cudaStreamNonBlocking));

@@ -201,3 +201,39 @@ def test_rows_stored_through_peer_pointers_equal_rows_out(engine, pkg):
         b.release()
     with pytest.raises(pkg.NbodyError):
         engine.bh_step_groups(pos, vel, 0.5, EPS, dt, 0, 1, rows_peers=[0])
+
+
+def test_replayed_graph_and_pending_rows_survive_other_calls(pkg):
+    """Two hazards of cached state.  (i) The fused direct step replays a captured graph at small sizes; a larger call in
+    between moves the scratch the graph points to, so the graph must be rebuilt, not replayed.  (ii) rows_in refers to the
+    permutation of the handle's last fused evaluation; any other Barnes-Hut evaluation on the handle overwrites it and the
+    rows must then be refused rather than scattered with the wrong permutation."""
+    import torch
+    I = pkg.integrators
+    eng = pkg.Engine(0, 1024)
+    dt = 1.0e-3
+    small_p, small_v = _state(pkg, 4096, 41)
+    big_p, big_v = _state(pkg, 150000, 43)
+    fresh = pkg.Engine(0, 4096)
+    want_p, want_v = small_p.clone(), small_v.clone()
+    for _ in range(3):
+        fresh.direct_step_slice(want_p, want_v, 2, EPS, dt, 0, 4096, pre_drift=(I.DRIFT_HALF_F64, 0.0), kick=(I.KICK_F32, 0.0),
+                                drift=(I.DRIFT_HALF_F64, 0.0))
+    p, v = small_p.clone(), small_v.clone()
+    kw = dict(pre_drift=(I.DRIFT_HALF_F64, 0.0), kick=(I.KICK_F32, 0.0), drift=(I.DRIFT_HALF_F64, 0.0))
+    eng.direct_step_slice(p, v, 2, EPS, dt, 0, 4096, **kw)              # captured
+    eng.direct_step_slice(p, v, 2, EPS, dt, 0, 4096, **kw)              # replayed
+    eng.direct_step_slice(big_p, big_v, 2, EPS, dt, 0, 150000, **kw)    # grows the partial-sum scratch
+    eng.direct_step_slice(p, v, 2, EPS, dt, 0, 4096, **kw)              # same arguments as the captured call
+    torch.cuda.synchronize()
+    assert torch.equal(p, want_p) and torch.equal(v, want_v)
+    # (ii)
+    pos, vel = _state(pkg, 8192, 47)
+    rows = torch.zeros(8192, 4, device="cuda")
+    eng.bh_step_groups(pos, vel, 0.5, EPS, dt, 0, 256, kick=(I.KICK_F32, 0.0), drift=(I.DRIFT_F32, 0.0), rows_out=rows)
+    acc = torch.zeros(8192, 4, device="cuda")
+    eng.bh_accel(pos, acc, 0.5, EPS)                                     # another evaluation: new permutation buffers
+    with pytest.raises(pkg.NbodyError):
+        eng.bh_step_groups(pos, vel, 0.5, EPS, dt, 0, 0, rows_in=rows, prev_drift=(I.DRIFT_F32, 0.0))
+    eng.close()
+    fresh.close()
