@@ -18,7 +18,8 @@ int nb_create(nb_context** out, int device, int max_bodies) {
     if (e != cudaSuccess || count == 0)
         return nb_fail(nullptr, NB_ERR_NO_DEVICE, "nb_create: no CUDA device (this engine has no CPU fallback)", e);
     if (device < 0 || device >= count) return nb_fail(nullptr, NB_ERR_INVALID, "nb_create: device out of range");
-    e = cudaSetDevice(device);
+    nb_device_guard guard;
+    e = guard.enter(device);
     if (e != cudaSuccess) return nb_fail(nullptr, NB_ERR_CUDA, "cudaSetDevice", e);
     cudaDeviceProp prop;
     e = cudaGetDeviceProperties(&prop, device);
@@ -40,7 +41,8 @@ int nb_create(nb_context** out, int device, int max_bodies) {
 
 int nb_destroy(nb_context* ctx) {
     if (!ctx) return NB_OK;
-    cudaSetDevice(ctx->device);
+    nb_device_guard guard;
+    guard.enter(ctx->device);
     cudaDeviceSynchronize();
     nb_bh_destroy(ctx);
     nb_bh3_destroy(ctx);
@@ -71,7 +73,7 @@ int nb_device_info(const nb_context* ctx, int* device, int* sm_count, uint64_t* 
 int nb_peer_alloc(nb_context* ctx, uint64_t bytes, void** ptr, unsigned char handle[64]) {
     if (!ctx || !ptr || !handle || bytes == 0) return ctx ? nb_fail(ctx, NB_ERR_INVALID, "nb_peer_alloc: bad argument") : NB_ERR_INVALID;
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     NB_CUDA(ctx, cudaMalloc(ptr, bytes));
     cudaIpcMemHandle_t h;
     cudaError_t e = cudaIpcGetMemHandle(&h, *ptr);
@@ -86,7 +88,7 @@ int nb_peer_alloc(nb_context* ctx, uint64_t bytes, void** ptr, unsigned char han
 
 int nb_peer_open(nb_context* ctx, const unsigned char handle[64], void** ptr) {
     if (!ctx || !ptr || !handle) return ctx ? nb_fail(ctx, NB_ERR_INVALID, "nb_peer_open: bad argument") : NB_ERR_INVALID;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, 64);
     NB_CUDA(ctx, cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
@@ -95,14 +97,14 @@ int nb_peer_open(nb_context* ctx, const unsigned char handle[64], void** ptr) {
 
 int nb_peer_close(nb_context* ctx, void* ptr) {
     if (!ctx) return NB_ERR_INVALID;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     if (ptr) NB_CUDA(ctx, cudaIpcCloseMemHandle(ptr));
     return NB_OK;
 }
 
 int nb_peer_free(nb_context* ctx, void* ptr) {
     if (!ctx) return NB_ERR_INVALID;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     if (ptr) NB_CUDA(ctx, cudaFree(ptr));
     return NB_OK;
 }
@@ -123,7 +125,7 @@ int nb_direct_accel_host(nb_context* ctx, const float* host_pos, float* host_acc
     if (!ctx) return NB_ERR_INVALID;
     if (n < 0 || (n > 0 && (!host_pos || !host_acc))) return nb_fail(ctx, NB_ERR_INVALID, "bad host buffers");
     if (n == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     size_t bytes = (size_t)n * 16;
     int rc = nb_reserve(ctx, &ctx->dev_pos, &ctx->dev_pos_bytes, bytes);
     if (rc) return rc;

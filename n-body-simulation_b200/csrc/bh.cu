@@ -99,6 +99,14 @@ struct nb_bh_state {
     GraphKey graph_key{};
     cudaGraphExec_t graph_exec = nullptr;
     cudaStream_t capture_stream = nullptr;
+    // the fused step (nb_bh_step_groups) at launch-bound sizes: a few captured graphs, matched on every argument of the
+    // call (a sharded stepper alternates between two rows arrays, a Forest-Ruth step between three coefficient sets)
+    struct StepGraph {
+        unsigned char key[320];
+        cudaGraphExec_t exec = nullptr;
+    };
+    StepGraph step_graphs[8];
+    int step_graph_next = 0;
     // the SFC sort (target order) and the tree-key sort + tree build do not depend on each other: the former runs on
     // a side stream between a fork and a join event (each radix pass fills only a fraction of the machine)
     cudaStream_t side_stream = nullptr;
@@ -1124,6 +1132,8 @@ int alloc(nb_context* ctx, T** p, size_t count) {
 void free_state(nb_bh_state* st) {
     if (!st) return;
     if (st->graph_exec) cudaGraphExecDestroy(st->graph_exec);
+    for (auto& g : st->step_graphs)
+        if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
     if (st->capture_stream) cudaStreamDestroy(st->capture_stream);
     if (st->h_full_flag) cudaFreeHost(st->h_full_flag);
     st->h_full_flag = st->d_full_flag = nullptr;
@@ -1403,7 +1413,7 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     const int groups = (n + 31) / 32;
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)
         return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 262144; }();
     const bool counting = (flags & NB_BH_COUNT_FLAG) != 0;
     rc = ensure_state(ctx, n);   // allocation must not happen inside a capture
@@ -1458,7 +1468,7 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     if (step->group_begin < 0 || step->group_count < 0 || step->group_begin + step->group_count > groups)
         return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
     if (step->flags & NB_BH_COUNT_WALK) return nb_fail(ctx, NB_ERR_INVALID, "the fused step has no instrumented walk");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     cudaStream_t stream = (cudaStream_t)stream_;
     rc = ensure_state(ctx, n);
     if (rc) return rc;
@@ -1495,6 +1505,47 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     epi.stats = step->stats_out;
     pick_sort_mode(st);
     st->perm_valid = false;
+    static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 262144; }();
+    const bool nothing_to_do = step->group_count == 0 && step->kick_kind == NB_KICK_NONE && step->drift_kind == NB_DRIFT_NONE;
+    if (n <= graph_max_n && n >= 2 && !nothing_to_do) {
+        // launch-bound sizes: replay a captured graph of the same call
+        struct Key {
+            const float* pos; const float* vel; int n, accumulate, sort_full, qcap, split; const void* perm; nb_bh_step st;
+        } key;
+        static_assert(sizeof(Key) <= sizeof(st->step_graphs[0].key), "step graph key storage");
+        memset(&key, 0, sizeof(key));
+        key.pos = pos; key.vel = vel; key.n = n;
+        key.accumulate = ((step->flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
+        key.sort_full = st->sort_full ? 1 : 0; key.qcap = walk_qcap(); key.split = walk_forced_split();
+        key.perm = prep.perm; key.st = *step;
+        nb_bh_state::StepGraph* hit = nullptr;
+        for (auto& g : st->step_graphs)
+            if (g.exec && memcmp(g.key, &key, sizeof(key)) == 0) hit = &g;
+        if (!hit) {
+            hit = &st->step_graphs[st->step_graph_next];
+            st->step_graph_next = (st->step_graph_next + 1) % 8;
+            if (hit->exec) { cudaGraphExecDestroy(hit->exec); hit->exec = nullptr; }
+            if (!st->capture_stream) NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->capture_stream, cudaStreamNonBlocking));
+            NB_CUDA(ctx, cudaStreamBeginCapture(st->capture_stream, cudaStreamCaptureModeThreadLocal));
+            rc = run_build(ctx, pos, n, step->flags, 4, step->theta, st->capture_stream, prep);
+            if (!rc && step->group_count > 0)
+                rc = run_walk(ctx, pos, step->acc_out, n, step->theta, eps, step->group_begin, step->group_count, false,
+                              st->capture_stream, epi);
+            cudaGraph_t graph = nullptr;
+            cudaError_t e = cudaStreamEndCapture(st->capture_stream, &graph);
+            if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+            if (e != cudaSuccess) return nb_fail(ctx, NB_ERR_CUDA, "cudaStreamEndCapture", e);
+            e = cudaGraphInstantiate(&hit->exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (e != cudaSuccess) { hit->exec = nullptr; return nb_fail(ctx, NB_ERR_CUDA, "cudaGraphInstantiate", e); }
+            memcpy(hit->key, &key, sizeof(key));
+        }
+        st->last_n = n;
+        st->bounds_valid = true;
+        NB_CUDA(ctx, cudaGraphLaunch(hit->exec, stream));
+        st->perm_valid = true;
+        return NB_OK;
+    }
     // nothing to walk, kick or drift: only the first kernel runs (it brings pos / vel up to date from rows_in).  A rank
     // that merely owns no groups still sorts: the next call needs this evaluation's permutation.
     const bool only_prep = step->group_count == 0 && step->kick_kind == NB_KICK_NONE && step->drift_kind == NB_DRIFT_NONE;
@@ -1517,7 +1568,7 @@ int nb_bh_accel_host(nb_context* ctx, const float* host_pos, float* host_acc, in
     if (!ctx) return NB_ERR_INVALID;
     if (n < 0 || (n > 0 && (!host_pos || !host_acc))) return nb_fail(ctx, NB_ERR_INVALID, "bad host buffers");
     if (n == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     const size_t bytes = (size_t)n * 16;
     int rc = nb_reserve(ctx, &ctx->dev_pos, &ctx->dev_pos_bytes, bytes);
     if (rc) return rc;
@@ -1536,7 +1587,7 @@ int nb_bh_stages_host(nb_context* ctx, const float* pos, int n, int flags, float
                       int32_t* sorted_idx, uint64_t* tree_keys) {
     if (!ctx) return NB_ERR_INVALID;
     if (n <= 0 || !pos) return nb_fail(ctx, NB_ERR_INVALID, "need n > 0 and a device pointer");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     int rc = run_build(ctx, pos, n, flags, 3, 1.0f, 0);
     if (rc) return rc;
     nb_bh_state* st = ctx->bh;
@@ -1560,7 +1611,7 @@ int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* 
     if (!ctx || !n_cells) return NB_ERR_INVALID;
     nb_bh_state* st = ctx->bh;
     if (!st || st->last_n < 1) return nb_fail(ctx, NB_ERR_INVALID, "no tree has been built on this handle");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     NB_CUDA(ctx, cudaDeviceSynchronize());
     const int n = st->last_n;
     if (n < 2) { *n_cells = 0; return NB_OK; }
@@ -1614,7 +1665,7 @@ int nb_bh_build_info(nb_context* ctx, int64_t info[4]) {
     if (!ctx || !info) return NB_ERR_INVALID;
     nb_bh_state* st = ctx->bh;
     if (!st || st->last_n < 1) return nb_fail(ctx, NB_ERR_INVALID, "no tree has been built on this handle");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     NB_CUDA(ctx, cudaDeviceSynchronize());
     const int n = st->last_n;
     int nodes = 0;
@@ -1641,7 +1692,7 @@ int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]) {
     if (!ctx || !counters) return NB_ERR_INVALID;
     nb_bh_state* st = ctx->bh;
     if (!st) return nb_fail(ctx, NB_ERR_INVALID, "no Barnes-Hut evaluation has run on this handle");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     NB_CUDA(ctx, cudaDeviceSynchronize());
     unsigned long long c[8];
     NB_CUDA(ctx, cudaMemcpy(c, st->counters, sizeof(c), cudaMemcpyDeviceToHost));

@@ -747,7 +747,7 @@ int nb_bh3d_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, f
     const int groups = (n + 31) / 32;
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)
         return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     cudaStream_t stream = (cudaStream_t)stream_;
     int rc = run_build3(ctx, pos, n, 4, theta, stream);
     if (rc) return rc;
@@ -781,7 +781,7 @@ int nb_bh3d_accel(nb_context* ctx, const float* pos, float* acc, int n, float th
 int nb_bh3d_stages_host(nb_context* ctx, const float* pos, int n, float* bounds6, uint64_t* tree_keys, int32_t* sorted_idx) {
     if (!ctx) return NB_ERR_INVALID;
     if (n <= 0 || !pos) return nb_fail(ctx, NB_ERR_INVALID, "need n > 0 and a device pointer");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     int rc = run_build3(ctx, pos, n, 3, 1.0f, 0);
     if (rc) return rc;
     nb_bh3_state* st = ctx->bh3;
@@ -807,7 +807,7 @@ int nb_bh3d_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t
     if (!ctx || !n_cells) return NB_ERR_INVALID;
     nb_bh3_state* st = ctx->bh3;
     if (!st || st->last_n < 1) return nb_fail(ctx, NB_ERR_INVALID, "no octree has been built on this handle");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     NB_CUDA(ctx, cudaDeviceSynchronize());
     const int n = st->last_n;
     if (n < 2) { *n_cells = 0; return NB_OK; }
@@ -860,7 +860,7 @@ int nb_bh3d_last_counters(nb_context* ctx, int64_t counters[6]) {
     if (!ctx || !counters) return NB_ERR_INVALID;
     nb_bh3_state* st = ctx->bh3;
     if (!st) return nb_fail(ctx, NB_ERR_INVALID, "no 3D Barnes-Hut evaluation has run on this handle");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     NB_CUDA(ctx, cudaDeviceSynchronize());
     unsigned long long c[8];
     NB_CUDA(ctx, cudaMemcpy(c, st->counters, sizeof(c), cudaMemcpyDeviceToHost));

@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) mufu_kernel(float* out, int iters) {
 
 extern "C" int nb_calibrate(nb_context* ctx, double out[4]) {
     if (!ctx || !out) return NB_ERR_INVALID;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     float* d_out = nullptr;
     long long* d_cyc = nullptr;
     NB_CUDA(ctx, cudaMalloc(&d_out, 16));

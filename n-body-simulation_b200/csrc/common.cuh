@@ -58,6 +58,26 @@ inline int nb_fail(nb_context* ctx, int code, const char* what, cudaError_t e = 
         if (e__ != cudaSuccess) return nb_fail((ctx), NB_ERR_CUDA, #call, e__); \
     } while (0)
 
+// Entry points run on the handle's device and leave the caller's current device as they found it (a process that drives
+// several GPUs -- or PyTorch, whose allocations follow the current device -- must not find it changed by a library call).
+struct nb_device_guard {
+    int prev = -1;
+    bool changed = false;
+    cudaError_t enter(int device) {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) return e;
+        if (prev == device) return cudaSuccess;
+        changed = true;
+        return cudaSetDevice(device);
+    }
+    ~nb_device_guard() {
+        if (changed) cudaSetDevice(prev);
+    }
+};
+#define NB_DEVICE(ctx)             \
+    nb_device_guard nb_dev_guard__; \
+    NB_CUDA((ctx), nb_dev_guard__.enter((ctx)->device))
+
 // Softening: the reference adds eps un-squared to r^2 and includes the self term, so eps = 0 turns every result into
 // 0 * inf = NaN (src/DirectComputeKernels.cu:23-30).  A floor of 1e-20 -- far below the FP32
 // resolution of any separation that is not itself zero -- keeps the self term at exactly 0 and changes nothing else.

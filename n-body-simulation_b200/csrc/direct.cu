@@ -417,7 +417,7 @@ static int direct_launch(nb_context* ctx, const float* pos, int n, int target_be
         return nb_fail(ctx, NB_ERR_INVALID, "target slice outside [0, n)");
     if (target_count == 0) return NB_OK;
     if (!pos || (!acc && !fused)) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
 
     const int ntiles = (n + TILE - 1) / TILE;
     int rc = NB_OK;

@@ -127,7 +127,7 @@ int nb_ic_standard(nb_context* ctx, float* pos, int offset, int count, uint64_t 
     if (!ctx) return NB_ERR_INVALID;
     if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     standard_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, offset, count, seed, cx, cy);
     NB_CUDA(ctx, cudaGetLastError());
     return NB_OK;
@@ -138,7 +138,7 @@ int nb_ic_standard_velocities(nb_context* ctx, const float* pos, const float* ac
     if (!ctx) return NB_ERR_INVALID;
     if (offset < 0 || count < 0 || (count > 0 && (!pos || !acc || !vel))) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     standard_velocity_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const float4*)pos, (const float4*)acc,
                                                                                    (float4*)vel, offset, count, seed, rotation);
     NB_CUDA(ctx, cudaGetLastError());
@@ -151,7 +151,7 @@ int nb_ic_uniform_ellipsoid(nb_context* ctx, float* pos, float* vel, int offset,
     if (!ctx) return NB_ERR_INVALID;
     if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     ellipsoid_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, offset, count, seed, cx, cy, rx,
                                                                            ry, z_half_height, mass, central_mass, vx, vy);
     NB_CUDA(ctx, cudaGetLastError());
@@ -165,7 +165,7 @@ int nb_ic_uniform_box(nb_context* ctx, float* pos, float* vel, int offset, int c
     if (offset < 0 || count < 0 || (count > 0 && !pos)) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     box_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, offset, count, seed, cx, cy, sx, sy,
                                                                      dim, mass_lo, mass_hi, speed_lo, speed_hi, vx, vy);
     NB_CUDA(ctx, cudaGetLastError());
@@ -178,7 +178,7 @@ int nb_ic_disk_velocities(nb_context* ctx, const float* pos, const float* acc, f
     if (begin < 0 || count < 0 || (count > 0 && (!pos || !acc || !vel))) return nb_fail(ctx, NB_ERR_INVALID, "bad range or null pointer");
     if (dim != 2 && dim != 3) return nb_fail(ctx, NB_ERR_INVALID, "dim must be 2 or 3");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     disk_velocity_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const float4*)pos, (const float4*)acc, (float4*)vel,
                                                                                begin, count, cx, cy, dim, bulk_vx, bulk_vy);
     NB_CUDA(ctx, cudaGetLastError());

@@ -53,7 +53,7 @@ int nb_verlet_dkd_drift(nb_context* ctx, float* pos, const float* vel, int begin
     if (!ctx) return NB_ERR_INVALID;
     if (begin < 0 || count < 0) return nb_fail(ctx, NB_ERR_INVALID, "bad slice");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     verlet_dkd_drift_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (const float4*)vel,
                                                                                   begin, count, dt);
     NB_CUDA(ctx, cudaGetLastError());
@@ -65,7 +65,7 @@ int nb_verlet_dkd_kick_drift(nb_context* ctx, float* pos, float* vel, const floa
     if (!ctx) return NB_ERR_INVALID;
     if (begin < 0 || count < 0) return nb_fail(ctx, NB_ERR_INVALID, "bad slice");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     verlet_dkd_kick_drift_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
         (float4*)pos, (float4*)vel, (const float4*)acc, begin, count, dt);
     NB_CUDA(ctx, cudaGetLastError());
@@ -117,7 +117,7 @@ extern "C" int nb_integrate_substep(nb_context* ctx, float* pos, float* vel, con
         return nb_fail(ctx, NB_ERR_INVALID, "unknown kick/drift kind");
     if (kick_kind == NB_KICK_MEAN_F64 && !acc_prev) return nb_fail(ctx, NB_ERR_INVALID, "NB_KICK_MEAN_F64 needs acc_prev");
     if (count == 0) return NB_OK;
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     SubstepArgs s{kick_kind, drift_kind, dt, kick_coef, drift_coef};
     substep_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>((float4*)pos, (float4*)vel, (const float4*)acc,
                                                                          (const float4*)acc_prev, begin, count, s);

@@ -96,7 +96,7 @@ extern "C" int nb_stats(nb_context* ctx, const float* pos, const float* vel, int
     out[0] = out[1] = out[2] = 0.0;
     if (target_count == 0) return NB_OK;
     if (!pos || !vel) return nb_fail(ctx, NB_ERR_INVALID, "null device pointer");
-    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_DEVICE(ctx);
     cudaStream_t stream = (cudaStream_t)stream_;
     const int pblocks = (target_count + ST_THREADS - 1) / ST_THREADS;
     const int kblocks = 64;   // the reference's launch shape (:13,15)

@@ -35,3 +35,7 @@ def test_engines_on_two_devices_in_one_process(pkg, oracle):
                 assert e3.max() < 5e-5 and np.median(eb) < 2e-6, (d, rep, e3.max(), np.median(eb))
     for eng in engines:
         eng.close()
+    # the calls on device 1 (and closing its engine) left the process's current device where they found it
+    assert torch.cuda.current_device() == 0
+    probe = torch.zeros(1).cuda()
+    assert probe.device.index == 0
