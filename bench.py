@@ -387,6 +387,7 @@ def main():
             v2 = torch.from_numpy(pkg.ics.disk_velocities(p2_h, a2.cpu().numpy())).to(dev)
             p2p = world > 1 and os.environ.get("NB_BH_P2P", "1") != "0"
             stepper = pkg.integrators.FusedBarnesHut(eng, p2, v2, "Verlet_DKD", THETA, EPS, world, rank, dist, p2p=p2p)
+            p2p = stepper.p2p      # False if the ranks could not map each other's memory (they then fall back together)
             coll_events = []
             if world > 1:
                 plain_gather = stepper._exchange

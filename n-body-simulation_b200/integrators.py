@@ -210,16 +210,36 @@ class FusedBarnesHut:
         self.force_evaluations = 0
         self.p2p = bool(p2p) and world > 1
         if self.p2p:
+            # every rank maps every other rank's two rows arrays; if any rank cannot (no peer access between the GPUs, no
+            # IPC between the processes), all ranks fall back to the all-gather together
             shape = (32 * self.groups, 4)
-            self._mine = [engine.peer_alloc(shape) for _ in range(2)]
+            ok, opened = 1, []
+            try:
+                self._mine = [engine.peer_alloc(shape) for _ in range(2)]
+                mine = [b.handle for b in self._mine]
+            except Exception:
+                ok, mine, self._mine = 0, [None, None], []
             handles = [None] * world
-            dist.all_gather_object(handles, [b.handle for b in self._mine])
-            self._peers = [[self._mine[k] if r == rank else engine.peer_open(handles[r][k], shape) for r in range(world)]
-                           for k in range(2)]
-            self._rows = [b.tensor for b in self._mine]
-            self._flip = 0
-            self._token = torch.zeros(1, device=pos.device)
-            dist.all_reduce(self._token)      # everyone has mapped everyone before the first store
+            dist.all_gather_object(handles, mine)
+            if ok and all(h[0] is not None for h in handles):
+                try:
+                    self._peers = [[self._mine[k] if r == rank else engine.peer_open(handles[r][k], shape)
+                                    for r in range(world)] for k in range(2)]
+                    opened = [b for row in self._peers for b in row if b.opened]
+                except Exception:
+                    ok = 0
+            else:
+                ok = 0
+            flag = torch.tensor([float(ok)], device=pos.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)      # also: everyone has mapped everyone before the first store
+            if flag.item() >= 1.0:
+                self._rows = [b.tensor for b in self._mine]
+                self._flip = 0
+                self._token = torch.zeros(1, device=pos.device)
+            else:
+                for b in opened + list(self._mine):
+                    b.release()
+                self.p2p = False
 
     def _exchange(self):
         """What follows a rank's walk: the all-gather of the rows, or (p2p) the barrier behind the peer stores."""
