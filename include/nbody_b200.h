@@ -63,6 +63,10 @@ extern "C" {
 #define NB_BH_ACCUMULATE_BOUNDS 1  /* reference behaviour: d_bounds is the running union over all calls,
                                       src/BarnesHutKernels.cu:190-193 + src/ComputeMethods.cpp:40 */
 
+#define NB_BH_PLANAR 0x200          /* nb_bh_step_groups, sharded form: the caller vouches that every body has v_z = 0 (the 2D path
+                                      never changes v_z), so z never moves and rows_in can be scattered without reading the
+                                      old positions and velocities back */
+
 #define NB_BH_COUNT_WALK 0x100      /* instrumented walk: also fills the counters of nb_bh_last_counters
                                       (nodes opened, children examined, ...); slower, for roofline accounting */
 

@@ -18,7 +18,7 @@ _lib = None
 
 NB_OK = 0
 NB_DIRECT_AUTO, NB_DIRECT_ORDERED, NB_DIRECT_NO_HOIST = 0, 1, 2
-NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS, NB_BH_COUNT_WALK = 0, 1, 0x100
+NB_BH_FRESH_BOUNDS, NB_BH_ACCUMULATE_BOUNDS, NB_BH_COUNT_WALK, NB_BH_PLANAR = 0, 1, 0x100, 0x200
 
 # every symbol include/nbody_b200.h declares (tests check that the library exports each one)
 ABI_SYMBOLS = [

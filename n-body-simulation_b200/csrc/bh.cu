@@ -131,6 +131,8 @@ struct PrepArgs {
     const int32_t* perm;
     SubstepArgs post;   // mode 2: drift of the previous evaluation's epilogue (applied to z here)
     SubstepArgs pre;    // modes 1, 2: drift before this evaluation (NB_DRIFT_NONE: none)
+    int planar;         // mode 2: the caller vouches for v_z = 0 everywhere, so z never moves: x, y, vx, vy are stored as two
+                        // 8-byte halves and nothing is read back (half the scattered traffic)
 };
 
 // What the walk does with a target's acceleration (nb_bh_step_groups): the kick and drift that follow the force
@@ -176,6 +178,17 @@ __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* par
         } else {
             const int body = prep.perm[i];
             const float4 r = prep.rows[i];
+            if (prep.planar) {
+                p.x = drift1g(prep.pre, r.x, r.z, 0.f);
+                p.y = drift1g(prep.pre, r.y, r.w, 0.f);
+                *reinterpret_cast<float2*>(&prep.pos_rw[body]) = make_float2(p.x, p.y);
+                *reinterpret_cast<float2*>(&prep.vel_rw[body]) = make_float2(r.z, r.w);
+                mnx = fminf(mnx, p.x);
+                mny = fminf(mny, p.y);
+                mxx = fmaxf(mxx, p.x);
+                mxy = fmaxf(mxy, p.y);
+                continue;
+            }
             p = prep.pos_rw[body];
             float4 v = prep.vel_rw[body];
             p.x = r.x; p.y = r.y; v.x = r.z; v.y = r.w;
@@ -1485,6 +1498,7 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
         prep.rows = reinterpret_cast<const float4*>(step->rows_in);
         prep.perm = st->idx32[st->sfc_sel];
         prep.post = SubstepArgs{NB_KICK_NONE, step->prev_drift_kind, step->dt, 0.0, step->prev_drift_coef};
+        prep.planar = (step->flags & NB_BH_PLANAR) ? 1 : 0;
     } else {
         prep.mode = step->pre_drift_kind != NB_DRIFT_NONE ? 1 : 0;
     }

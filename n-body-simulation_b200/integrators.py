@@ -196,6 +196,8 @@ class FusedBarnesHut:
         self.n = pos.shape[0]
         self.integrator, self.theta, self.eps, self.flags = integrator, theta, softening, flags
         self.world, self.rank, self.dist = world, rank, dist
+        if world > 1 and not bool((vel[:, 2] != 0).any().item()):
+            self.flags |= 0x200      # NB_BH_PLANAR: v_z = 0 everywhere and the 2D path keeps it so -- z never moves
         self.groups = (self.n + 31) // 32
         self.g0, self.g1 = shard.group_bounds(self.n, world, rank)
         self._bounds = [shard.group_bounds(self.n, world, r) for r in range(world)]

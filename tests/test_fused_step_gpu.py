@@ -46,18 +46,21 @@ def test_fused_in_place_equals_separate_kernels(engine, pkg, name):
     assert fused.force_evaluations == steps * len(pkg.integrators.stepper_program(name, dt)[1])
 
 
+@pytest.mark.parametrize("planar", [False, True])
 @pytest.mark.parametrize("name,world,n", [("Verlet_DKD", 3, 20000), ("PEFRL", 2, 8192), ("ForestRuth", 4, 5000),
                                           ("Euler_Symplectic_DK", 8, 12345), ("Euler_Symplectic_KD", 2, 33)])
-def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n):
+def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n, planar):
     """`world` ranks emulated on one GPU (one engine and one replica of pos / vel each; the all-gather is a
     concatenation of the ranks' rows): after every step each replica equals the single-GPU trajectory bit for bit,
-    for even and ragged group counts, with v_z carried through.  (Sizes at which one GPU and a rank choose the same
+    for even and ragged group counts, with v_z carried through -- or, `planar`, with v_z = 0 and NB_BH_PLANAR, which scatters
+    the rows without reading the old state back.  (Sizes at which one GPU and a rank choose the same
     number of warps per group; a different choice changes the order of a target's FP32 sum -- profiles/multigpu_check.py
     pins it with NB_BH_WALK_SPLIT=1 for its two-rank comparison.)"""
     import torch
     I = pkg.integrators
     dt, steps = 1.0e-3, 2
-    pos, vel = _state(pkg, n, 11, vz=True)
+    pos, vel = _state(pkg, n, 11, vz=not planar)
+    flags = pkg.NB_BH_PLANAR if planar else 0
     want_p, want_v = _classic(pkg, engine, name, pos, vel, dt, steps)
     groups = (n + 31) // 32
     ranks = []
@@ -74,13 +77,14 @@ def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n):
                 rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, rk["g0"], rk["g1"] - rk["g0"],
                                          pre_drift=pre if k == 0 else (0, 0.0), kick=kick, drift=drift,
                                          rows_in=rows_all if pending is not None else None,
-                                         prev_drift=pending if pending is not None else (0, 0.0), rows_out=rk["rows_out"])
+                                         prev_drift=pending if pending is not None else (0, 0.0), rows_out=rk["rows_out"],
+                                         flags=flags)
             torch.cuda.synchronize()
             for rk in ranks:                                  # the all-gather
                 rows_all[32 * rk["g0"]:32 * rk["g1"]] = rk["rows_out"][:32 * (rk["g1"] - rk["g0"])]
             pending = drift
     for rk in ranks:                                          # materialize
-        rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, 0, 0, rows_in=rows_all, prev_drift=pending)
+        rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, 0, 0, rows_in=rows_all, prev_drift=pending, flags=flags)
     torch.cuda.synchronize()
     for rk in ranks:
         assert torch.equal(rk["pos"], want_p) and torch.equal(rk["vel"], want_v)
