@@ -759,6 +759,11 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) walk_kernel(const float4* __r
 #define NB_WALK_UNROLL 8
 #endif
 constexpr int WL_UNROLL = NB_WALK_UNROLL;   // packed pairs per iteration of the list evaluation
+#ifndef NB_WALK_MINB
+#define NB_WALK_MINB 7
+#endif
+constexpr int WL_MINB = NB_WALK_MINB;   // resident blocks per SM the walk is compiled for: 7 = 72 registers per thread (measured
+                                        // against 8 / 6 / 5: 1.160 / 1.149 / 1.197 ms per evaluation, 7: 1.119)
 constexpr int WL_WARPS = 4;
 constexpr int WL_QCAP = 1024;   // node ids per group (measured peak at N = 1M, theta = 0.5: see bench counters)
 constexpr int WL_LCAP = 64;     // pending accepted records per group
@@ -773,7 +778,7 @@ constexpr int WL_DFS_ROOM = 128;
 // SPLIT-th node (the others discard what they summed so far) and walks its share; the partial sums are added in
 // warp order, so the result stays deterministic.
 template <bool COUNT, int SPLIT>
-__global__ void __launch_bounds__(WL_WARPS * 32, 8) walk_lists_kernel(const float4* __restrict__ pos,
+__global__ void __launch_bounds__(WL_WARPS * 32, WL_MINB) walk_lists_kernel(const float4* __restrict__ pos,
                                                                   const int32_t* __restrict__ sorted_idx, int n,
                                                                   const float4* __restrict__ cblk,
                                                                   const uint32_t* __restrict__ clink,   // 4 links per node
