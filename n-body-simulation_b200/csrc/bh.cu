@@ -260,8 +260,14 @@ __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* par
 // keys: SFC key (src/BarnesHutKernels.cu:197-240, strict '>') and 64-bit tree-path key (the '>=' descent of
 // :266-285, digit = path ^ 2 so that both orders agree away from exact midpoint hits)
 // ------------------------------------------------------------------------------------------------------
-constexpr int KEYS_THREADS = 256;
-constexpr int KEYS_PER_BLOCK = 4096;
+#ifndef NB_KEYS_THREADS
+#define NB_KEYS_THREADS 256
+#endif
+#ifndef NB_KEYS_PER_BLOCK
+#define NB_KEYS_PER_BLOCK 1024
+#endif
+constexpr int KEYS_THREADS = NB_KEYS_THREADS;
+constexpr int KEYS_PER_BLOCK = NB_KEYS_PER_BLOCK;
 constexpr int N_DIGITS = 12;   // 4 digits of the 32-bit SFC key, then 8 digits of the 64-bit tree key
 
 __global__ void __launch_bounds__(KEYS_THREADS) keys_kernel(const float4* __restrict__ pos, int n,
