@@ -162,6 +162,11 @@ int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* 
  * depth-first order -- slower, same result; the counters [0..3] need NB_BH_COUNT_WALK, the status bit does not). */
 int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]);
 
+/* Per-group work of the last NB_BH_COUNT_WALK evaluation: work[g] = records summed for each target of group g (bodies and
+ * accepted cells; host int32[ceil(n/32)]).  The spread max / mean over groups -- and over blocks of four consecutive
+ * groups, the unit the kernel schedules -- is the walk's load imbalance (profiles/bh_counters.py).  Synchronises. */
+int nb_bh_group_work(nb_context* ctx, int32_t* work, int groups);
+
 /* Facts about the tree built by the last nb_bh_* call (synchronises; tests and profiling): info[0] = nodes,
  * info[1] = bodies the five-pass tree-key sort left to its repair block (runs sharing the upper 40 key bits),
  * info[2] = bit 0: the repair block overflowed and the conditional full sort ran on the device, bit 1: the host had

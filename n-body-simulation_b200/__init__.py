@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "nb_direct_accel", "nb_direct_accel_slice", "nb_direct_accel_host", "nb_direct_accel_noalloc",
     "nb_direct_last_launch", "nb_direct_step_slice",
     "nb_bh_accel", "nb_bh_accel_groups", "nb_bh_accel_host", "nb_bh_stages_host", "nb_bh_export_tree",
-    "nb_bh_last_counters", "nb_bh_build_info", "nb_bh_step_groups", "nb_peer_alloc", "nb_peer_open", "nb_peer_close",
+    "nb_bh_last_counters", "nb_bh_group_work", "nb_bh_build_info", "nb_bh_step_groups", "nb_peer_alloc", "nb_peer_open", "nb_peer_close",
     "nb_peer_free", "nb_calibrate", "nb_verlet_dkd_drift", "nb_verlet_dkd_kick_drift",
     "nb_integrate_substep", "nb_stats", "nb_ic_uniform_ellipsoid", "nb_ic_uniform_box", "nb_ic_disk_velocities", "nb_ic_standard", "nb_ic_standard_velocities",
     "nb_bh3d_accel", "nb_bh3d_accel_groups", "nb_bh3d_stages_host", "nb_bh3d_export_tree", "nb_bh3d_last_counters",
@@ -112,6 +112,7 @@ def lib():
         L.nb_bh_export_tree.argtypes = [vp, C.POINTER(i), vp, vp, vp, vp, vp, vp]
         L.nb_bh_last_counters.argtypes = [vp, C.POINTER(C.c_int64)]
         L.nb_bh_build_info.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.nb_bh_group_work.argtypes = [vp, vp, i]
         L.nb_bh_step_groups.argtypes = [vp, vp, vp, i, C.POINTER(BHStep), vp]
         L.nb_peer_alloc.argtypes = [vp, C.c_uint64, C.POINTER(vp), C.c_char_p]
         L.nb_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
@@ -285,6 +286,12 @@ class Engine:
                 st.rows_peers[k] = ptr
         self._check(lib().nb_bh_step_groups(self._h, pos.data_ptr(), vel.data_ptr(), n, C.byref(st), _stream_ptr(stream)),
                     "nb_bh_step_groups")
+
+    def bh_group_work(self, n):
+        """Records summed per target, group by group, in the last NB_BH_COUNT_WALK evaluation (int32 [ceil(n/32)])."""
+        w = np.zeros((n + 31) // 32, np.int32)
+        self._check(lib().nb_bh_group_work(self._h, w.ctypes.data, w.shape[0]), "nb_bh_group_work")
+        return w
 
     def peer_alloc(self, shape):
         """float32 device buffer of `shape` that other ranks can map; returns a PeerBuffer (handle = 64 bytes to send)."""

@@ -82,6 +82,7 @@ struct nb_bh_state {
     float4* root_rec = nullptr;        // the root cell as a child record (cx, cy, m, link)
     unsigned long long* counters = nullptr;  // opened, examined, interactions, max stack, overflow flag
     int last_n = 0;
+    int group_work_n = 0;      // > 0: ext_a holds the per-group record counts of an instrumented walk over that many bodies
     bool perm_valid = false;   // the SFC permutation of the last evaluation is intact (nb_bh_step_groups: rows_in)
     // result locations of the last sorts
     int sfc_sel = 0, tree_sel = 0;
@@ -792,7 +793,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, WL_MINB) walk_lists_kernel(cons
                                                                   const float4* __restrict__ root_rec, float eps,
                                                                   int group_begin, int group_count, float4* __restrict__ acc,
                                                                   unsigned long long* __restrict__ counters, int qcap,
-                                                                  const WalkEpilogue epi) {
+                                                                  const WalkEpilogue epi, int32_t* __restrict__ group_work) {
     __shared__ uint32_t q_s[WL_WARPS][WL_QCAP];
     // pending accepted records, two per slot so that the evaluation runs on FP32x2: (cx0, cx1, cy0, cy1) and (m0, m1)
     __shared__ float4 lxy_s[WL_WARPS][WL_LCAP / 2];
@@ -1110,6 +1111,7 @@ __global__ void __launch_bounds__(WL_WARPS * 32, WL_MINB) walk_lists_kernel(cons
         atomicMax(&counters[3], (unsigned long long)c_depth);
     }
     if (COUNT && valid) atomicAdd(&counters[2], c_inter);   // lane interactions: per valid target
+    if (COUNT && lane == 0 && group_work) atomicAdd(&group_work[group_begin + g], (int)c_inter);   // records this group summed
 }
 
 __global__ void zero_acc_kernel(float4* acc, int n) {
@@ -1266,6 +1268,7 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
     const float4* pos = reinterpret_cast<const float4*>(pos_);
     st->last_n = n;
     if (upto >= 3) st->perm_valid = false;   // the sorts below overwrite the permutation a pending rows_in refers to
+    if (upto >= 4) st->group_work_n = 0;     // ... and the tree stage the per-group counts of an earlier instrumented walk
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
     int bblocks = std::min(1024, std::max(1, (n + 1023) / 1024));
     bounds_kernel<<<bblocks, 256, 0, stream>>>(pos, n, st->bounds_part, st->ticket, st->bounds, accumulate, st->counters + 4, prep);
@@ -1371,7 +1374,12 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
     }
     static const int use_dfs = [] { const char* v = getenv("NB_BH_WALK"); return (v && v[0] == 'd') ? 1 : 0; }();
     if (use_dfs && epi.mode != 0) return nb_fail(ctx, NB_ERR_INVALID, "NB_BH_WALK=dfs has no fused kick/drift epilogue");
-    if (count) cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
+    if (count) {
+        cudaMemsetAsync(st->counters, 0, 8 * sizeof(unsigned long long), stream);
+        // per-group work of the instrumented walk lands in ext_a, which the tree stage no longer needs once emit has run
+        cudaMemsetAsync(st->ext_a, 0, (size_t)((n + 31) / 32) * sizeof(int32_t), stream);
+        st->group_work_n = n;
+    }
     if (use_dfs) {   // depth-first walk in the reference's own order (kept for comparison: NB_BH_WALK=dfs)
         const int blocks = (group_count + WALK_WARPS - 1) / WALK_WARPS;
         if (count)
@@ -1392,7 +1400,8 @@ int run_walk(nb_context* ctx, const float* pos_, float* acc_, int n, float theta
 #define NB_LAUNCH_WALK(COUNTING, SPLIT)                                                                               \
     walk_lists_kernel<COUNTING, SPLIT><<<blocks, WL_WARPS * 32, 0, stream>>>(pos, st->idx32[st->sfc_sel], n, st->cblk, links, \
                                                                             st->spos, st->root_rec, eps, group_begin,         \
-                                                                            group_count, acc, st->counters, qcap, epi)
+                                                                            group_count, acc, st->counters, qcap, epi,   \
+                                                                            count ? st->ext_a : nullptr)
         if (count) {
             if (split == 1) NB_LAUNCH_WALK(true, 1); else if (split == 2) NB_LAUNCH_WALK(true, 2); else NB_LAUNCH_WALK(true, 4);
         } else {
@@ -1710,6 +1719,18 @@ int nb_bh_build_info(nb_context* ctx, int64_t info[4]) {
     info[1] = words[0];
     info[2] = (words[1] ? 1 : 0) | (st->sort_full ? 2 : 0);
     info[3] = deepest;
+    return NB_OK;
+}
+
+int nb_bh_group_work(nb_context* ctx, int32_t* work, int groups) {
+    if (!ctx || !work) return NB_ERR_INVALID;
+    nb_bh_state* st = ctx->bh;
+    if (!st || st->group_work_n <= 0 || st->group_work_n != st->last_n)
+        return nb_fail(ctx, NB_ERR_INVALID, "the last evaluation on this handle was not an NB_BH_COUNT_WALK one");
+    if (groups != (st->group_work_n + 31) / 32) return nb_fail(ctx, NB_ERR_INVALID, "groups must be ceil(n / 32)");
+    NB_DEVICE(ctx);
+    NB_CUDA(ctx, cudaDeviceSynchronize());
+    NB_CUDA(ctx, cudaMemcpy(work, st->ext_a, (size_t)groups * sizeof(int32_t), cudaMemcpyDeviceToHost));
     return NB_OK;
 }
 

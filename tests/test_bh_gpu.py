@@ -391,6 +391,11 @@ def test_cold_collapse_one_million(pkg, oracle):
     info = eng.bh_build_info()
     assert k["status"] == 0 and k["max_stack"] <= 896, k
     assert 0 < info["nodes"] < n and 20 <= info["deepest_level"] <= 32, info
+    work = eng.bh_group_work(n).astype(np.int64)             # records each target of a group summed
+    assert int(work.sum()) * 32 == k["interactions"]
+    blocks = work.reshape(-1, 4).sum(axis=1)                  # four consecutive groups share a thread block
+    imbalance = {"group_max_over_mean": float(work.max() / work.mean()), "block_max_over_mean": float(blocks.max() / blocks.mean()),
+                 "group_p99_over_mean": float(np.quantile(work, 0.99) / work.mean())}
     sample = np.arange(0, n, n // 512)[:512]
     got = acc.cpu().numpy()[sample]
     ref = np.concatenate([oracle.direct_f64(pos, 2, EPS, t0=int(t), nt=1) for t in sample])
@@ -404,6 +409,6 @@ def test_cold_collapse_one_million(pkg, oracle):
     if os.path.isdir(out):
         import json
         with open(os.path.join(out, "cold_collapse_1m.json"), "w") as f:
-            json.dump({"counters": k, "build": info, "theta_error_vs_fp64": {"median": float(np.median(e)),
+            json.dump({"counters": k, "build": info, "walk_imbalance": imbalance, "theta_error_vs_fp64": {"median": float(np.median(e)),
                        "p99": float(np.quantile(e, 0.99)), "max": float(e.max())}}, f, indent=1)
     eng.close()
