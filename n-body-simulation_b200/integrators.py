@@ -210,7 +210,7 @@ class FusedBarnesHut:
         self.stats_buf = torch.zeros(2 * self.groups, dtype=torch.float64, device=pos.device) if stats else None
         self.pending = None          # ((drift kind, coefficient), dt) of the evaluation whose rows are waiting in rows_all
         self.force_evaluations = 0
-        self.p2p = bool(p2p) and world > 1
+        self.p2p = bool(p2p) and 1 < world <= 8      # NB_MAX_PEERS pointers fit in one nb_bh_step
         if self.p2p:
             # every rank maps every other rank's two rows arrays; if any rank cannot (no peer access between the GPUs, no
             # IPC between the processes), all ranks fall back to the all-gather together
@@ -242,6 +242,14 @@ class FusedBarnesHut:
                 for b in opened + list(self._mine):
                     b.release()
                 self.p2p = False
+
+    def close(self):
+        """Unmaps the other ranks' rows arrays and frees this rank's (p2p); call on every rank before the engine goes."""
+        if self.p2p:
+            for row in self._peers:
+                for b in row:
+                    b.release()
+            self.p2p = False
 
     def _exchange(self):
         """What follows a rank's walk: the all-gather of the rows, or (p2p) the barrier behind the peer stores."""
