@@ -462,166 +462,9 @@ __device__ __forceinline__ int cpl(uint64_t a, uint64_t b) {  // common prefix, 
     return x ? (__clzll((long long)x) >> 1) : MAX_LEVEL;
 }
 
-// smallest a in [0, i] with cpl(K[a], K[i]) >= L
-__device__ __forceinline__ int left_extent(const uint64_t* __restrict__ K, int i, int L) {
-    const uint64_t ki = K[i];
-    int good = i, step = 1;
-    while (good - step >= 0 && cpl(K[good - step], ki) >= L) { good -= step; step <<= 1; }
-    int bad = good - step;
-    if (bad < -1) bad = -1;
-    while (good - bad > 1) {
-        const int mid = (good + bad) >> 1;
-        if (cpl(K[mid], ki) >= L) good = mid; else bad = mid;
-    }
-    return good;
-}
-// largest b in [i, limit] with cpl(K[i], K[b]) >= L
-__device__ __forceinline__ int right_extent(const uint64_t* __restrict__ K, int i, int limit, int L) {
-    const uint64_t ki = K[i];
-    int good = i, step = 1;
-    while (good + step <= limit && cpl(ki, K[good + step]) >= L) { good += step; step <<= 1; }
-    int bad = good + step;
-    if (bad > limit + 1) bad = limit + 1;
-    while (bad - good > 1) {
-        const int mid = (good + bad) >> 1;
-        if (cpl(ki, K[mid]) >= L) good = mid; else bad = mid;
-    }
-    return good;
-}
-
-// Every boundary i (between sorted bodies i and i+1) is a separator between two children of exactly one node:
-// the node at level L = cpl(K[i], K[i+1]).  Three extents describe its neighbourhood:
-//   A = first body of that node,  C = first body of the child that ends at i,  R = last body of the child that
-//   starts at i+1.
-// i is the node's first separator ("leader", gives the node its id) iff C == A.
-// With d(j) = cpl(K[j], K[j+1]) the three are runs of d: C = start of the run of d >= L+1 that ends at i, A = start of the
-// run of d >= L it continues into, R = end of the run of d >= L+1 that starts at i+1.  A block keeps d of its 2048
-// separators in shared memory together with the minima over every aligned-by-start power-of-two window (12 x 2 KB), so a
-// run is walked in 12 uniform steps -- take the window if its minimum still clears the level -- with no divergence
-// between lanes; only a run that reaches the edge of the chunk goes on with the galloping key comparisons of
-// left_extent / right_extent (a few separators per chunk: those of nodes that straddle it).
-constexpr int BND_LOG = SCAN_SHIFT;   // 2^11 separators per block
-
-// continue a leftward / rightward run in global memory from a body known to be inside it
-__device__ __forceinline__ int left_extent_from(const uint64_t* __restrict__ K, int good, uint64_t ki, int L) {
-    int step = 1;
-    while (good - step >= 0 && cpl(K[good - step], ki) >= L) { good -= step; step <<= 1; }
-    int bad = good - step;
-    if (bad < -1) bad = -1;
-    while (good - bad > 1) {
-        const int mid = (good + bad) >> 1;
-        if (cpl(K[mid], ki) >= L) good = mid; else bad = mid;
-    }
-    return good;
-}
-__device__ __forceinline__ int right_extent_from(const uint64_t* __restrict__ K, int good, int limit, uint64_t ki, int L) {
-    int step = 1;
-    while (good + step <= limit && cpl(ki, K[good + step]) >= L) { good += step; step <<= 1; }
-    int bad = good + step;
-    if (bad > limit + 1) bad = limit + 1;
-    while (bad - good > 1) {
-        const int mid = (good + bad) >> 1;
-        if (cpl(ki, K[mid]) >= L) good = mid; else bad = mid;
-    }
-    return good;
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS) boundary_kernel(const uint64_t* __restrict__ K, int n,
-                                                               int32_t* __restrict__ ext_a, int32_t* __restrict__ ext_c,
-                                                               int32_t* __restrict__ ext_r, int32_t* __restrict__ flag_scan,
-                                                               int32_t* __restrict__ tot) {
-    // T[k][j] = 1 + min d over separators [j, j + 2^k) of this chunk (0 where no separator exists: stops every run)
-    __shared__ __align__(16) uint8_t T[BND_LOG + 1][SCAN_CHUNK];
-    const int base = blockIdx.x * SCAN_CHUNK;
-    const int j0 = threadIdx.x * SCAN_ITEMS;
-    {
-        uint64_t kprev = base + j0 < n ? K[base + j0] : 0ull;
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; k++) {
-            const int i = base + j0 + k;
-            uint8_t lev = 0;
-            if (i < n - 1) {
-                const uint64_t knext = K[i + 1];
-                lev = (uint8_t)(cpl(kprev, knext) + 1);
-                kprev = knext;
-            }
-            T[0][j0 + k] = lev;
-        }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 1; k <= BND_LOG; k++) {
-        const int half = 1 << (k - 1);
-        if (half >= 4) {   // eight bytes at a time: two packed unsigned byte minima
-            const uint2 lo = *reinterpret_cast<const uint2*>(&T[k - 1][j0]);
-            uint2 hi = make_uint2(0u, 0u);
-            if (j0 + half < SCAN_CHUNK) hi = *reinterpret_cast<const uint2*>(&T[k - 1][j0 + half]);
-            *reinterpret_cast<uint2*>(&T[k][j0]) = make_uint2(__vminu4(lo.x, hi.x), __vminu4(lo.y, hi.y));
-        } else {
-#pragma unroll
-            for (int t = 0; t < SCAN_ITEMS; t++) {
-                const int j = j0 + t;
-                const uint8_t lo = T[k - 1][j];
-                const uint8_t hi = j + half < SCAN_CHUNK ? T[k - 1][j + half] : (uint8_t)0;
-                T[k][j] = lo < hi ? lo : hi;
-            }
-        }
-        __syncthreads();
-    }
-    // the thread's eight separators advance together, one window size at a time: sixteen independent chains of
-    // shared-memory loads instead of one long dependent one
-    int v[SCAN_ITEMS], pc[SCAN_ITEMS], pa[SCAN_ITEMS], pr[SCAN_ITEMS];
-    uint8_t v1[SCAN_ITEMS];   // threshold for d >= L+1 in the +1 coding; d >= L is v1 - 1
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        v1[k] = (uint8_t)(T[0][j0 + k] + 1);   // = L + 2 (1 for a slot without separator: its runs are never used)
-        pc[k] = j0 + k;
-        pr[k] = j0 + k + 1;
-    }
-#pragma unroll
-    for (int b = BND_LOG; b >= 0; b--) {
-        const int w = 1 << b;
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; k++) {
-            if (pc[k] - w >= 0 && T[b][pc[k] - w] >= v1[k]) pc[k] -= w;          // run of d >= L+1 ending at the separator
-            if (pr[k] + w <= SCAN_CHUNK && T[b][pr[k]] >= v1[k]) pr[k] += w;     // run of d >= L+1 starting behind it
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) pa[k] = pc[k];
-#pragma unroll
-    for (int b = BND_LOG; b >= 0; b--) {
-        const int w = 1 << b;
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; k++)
-            if (pa[k] - w >= 0 && T[b][pa[k] - w] >= v1[k] - 1) pa[k] -= w;      // ... continued as a run of d >= L
-    }
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        const int j = j0 + k, i = base + j;
-        int f = 0;
-        if (i < n - 1) {
-            const int L = (int)v1[k] - 2;
-            int c = base + pc[k], a = base + pa[k], r = base + pr[k];
-            // a run that reached the edge of the chunk may go on beyond it
-            if ((pc[k] == 0 || pa[k] == 0) && base > 0) {
-                const uint64_t ki = K[i];
-                if (pc[k] == 0) c = left_extent_from(K, c, ki, L + 1);
-                a = left_extent_from(K, pc[k] == 0 ? c : a, ki, L);
-            }
-            if (pr[k] == SCAN_CHUNK && r < n - 1) r = right_extent_from(K, r, n - 1, K[i + 1], L + 1);
-            ext_a[i] = a;
-            ext_c[i] = c;
-            ext_r[i] = r;
-            f = (c == a);
-        }
-        v[k] = f;
-    }
-    block_scan_chunk<int>(v, &tot[blockIdx.x]);
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++)
-        if (base + j0 + k < n - 1) flag_scan[base + j0 + k] = v[k];
-}
+struct Level2 {   // common prefix of two tree keys in quadtree levels, for the shared boundary kernel
+    static __device__ __forceinline__ int of(uint64_t a, uint64_t b) { return cpl(a, b); }
+};
 
 struct TreeView {
     const uint64_t* K;
@@ -1426,7 +1269,7 @@ int run_build(nb_context* ctx, const float* pos_, int n, int flags, int upto, fl
         scan_totals_kernel<D3><<<1, 1024, 0, sums_stream>>>(st->psum_blk, chunks);
         if (fork) cudaEventRecord(st->join_ev, st->side_stream);
         const int bchunks = (n - 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
-        boundary_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk);
+        boundary_kernel<Level2><<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk);
         scan_totals_kernel<int><<<1, 1024, 0, stream>>>(st->flag_blk, bchunks);
         if (fork) NB_CUDA(ctx, cudaStreamWaitEvent(stream, st->join_ev, 0));
         TreeView tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, st->ext_a, st->ext_c, st->ext_r, n};

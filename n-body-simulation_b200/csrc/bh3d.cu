@@ -200,60 +200,9 @@ __device__ __forceinline__ int cpl3(uint64_t a, uint64_t b) {   // common prefix
     const uint64_t x = a ^ b;
     return x ? ((__clzll((long long)x) - 1) / 3) : MAXL3;
 }
-__device__ __forceinline__ int left_extent3(const uint64_t* __restrict__ K, int i, int L, int start) {
-    const uint64_t ki = K[i];
-    int good = start, step = 1;
-    while (good - step >= 0 && cpl3(K[good - step], ki) >= L) { good -= step; step <<= 1; }
-    int bad = good - step;
-    if (bad < -1) bad = -1;
-    while (good - bad > 1) {
-        const int mid = (good + bad) >> 1;
-        if (cpl3(K[mid], ki) >= L) good = mid; else bad = mid;
-    }
-    return good;
-}
-__device__ __forceinline__ int right_extent3(const uint64_t* __restrict__ K, int i, int limit, int L) {
-    const uint64_t ki = K[i];
-    int good = i, step = 1;
-    while (good + step <= limit && cpl3(ki, K[good + step]) >= L) { good += step; step <<= 1; }
-    int bad = good + step;
-    if (bad > limit + 1) bad = limit + 1;
-    while (bad - good > 1) {
-        const int mid = (good + bad) >> 1;
-        if (cpl3(ki, K[mid]) >= L) good = mid; else bad = mid;
-    }
-    return good;
-}
-
-// per separator i: A = first body of its node, C = first body of the child ending at i, R = last body of the child
-// starting at i+1; leader (numbers the node) iff C == A.
-__global__ void __launch_bounds__(SCAN_THREADS) boundary3_kernel(const uint64_t* __restrict__ K, int n,
-                                                                int32_t* __restrict__ ext_a, int32_t* __restrict__ ext_c,
-                                                                int32_t* __restrict__ ext_r, int32_t* __restrict__ flag_scan,
-                                                                int32_t* __restrict__ tot) {
-    int v[SCAN_ITEMS];
-    const int i0 = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        const int i = i0 + k;
-        int f = 0;
-        if (i < n - 1) {
-            const int L = cpl3(K[i], K[i + 1]);
-            const int c = left_extent3(K, i, L + 1, i);
-            const int a = left_extent3(K, i, L, c);
-            const int r = right_extent3(K, i + 1, n - 1, L + 1);
-            ext_a[i] = a;
-            ext_c[i] = c;
-            ext_r[i] = r;
-            f = (c == a);
-        }
-        v[k] = f;
-    }
-    block_scan_chunk<int>(v, &tot[blockIdx.x]);
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++)
-        if (i0 + k < n - 1) flag_scan[i0 + k] = v[k];
-}
+struct Level3 {   // common prefix of two octree keys in levels, for the shared boundary kernel (bh_shared.cuh)
+    static __device__ __forceinline__ int of(uint64_t a, uint64_t b) { return cpl3(a, b); }
+};
 
 struct TreeView3 {
     const uint64_t* K;
@@ -712,7 +661,7 @@ int run_build3(nb_context* ctx, const float* pos_, int n, int upto, float theta,
         gather_scan3_kernel<<<chunks, SCAN_THREADS, 0, stream>>>(pos, st->idx[st->sel], n, st->spos, st->psum, st->psum_blk);
         scan_totals_kernel<D4><<<1, 1024, 0, stream>>>(st->psum_blk, chunks);
         const int bchunks = (n - 1 + SCAN_CHUNK - 1) / SCAN_CHUNK;
-        boundary3_kernel<<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk);
+        boundary_kernel<Level3><<<bchunks, SCAN_THREADS, 0, stream>>>(K, n, st->ext_a, st->ext_c, st->ext_r, st->flag_scan, st->flag_blk);
         scan_totals_kernel<int><<<1, 1024, 0, stream>>>(st->flag_blk, bchunks);
         TreeView3 tv{K, st->spos, st->psum, st->psum_blk, st->flag_scan, st->flag_blk, st->ext_a, st->ext_c, st->ext_r, n};
         emit3_kernel<<<(n - 1 + 255) / 256, 256, 0, stream>>>(tv, st->bounds, theta, st->crec, st->cthr, st->clink, st->node_first,
