@@ -46,9 +46,39 @@ def test_fused_in_place_equals_separate_kernels(engine, pkg, name):
     assert fused.force_evaluations == steps * len(pkg.integrators.stepper_program(name, dt)[1])
 
 
+@pytest.mark.parametrize("name", ["Verlet_DKD", "PEFRL"])
+def test_fused_step_above_the_eager_capture_size(pkg, name):
+    """Above 262,144 bodies an argument set is run directly the first time and captured into a graph only when it
+    returns: four steps cross first sighting, capture and replay, and must still equal the separate kernels."""
+    import torch
+    n, dt, steps = 300000, 1.0e-3, 4
+    eng = pkg.Engine(0, n)
+    pos, vel = _state(pkg, n, 17)
+    want_p, want_v = _classic(pkg, eng, name, pos, vel, dt, steps)
+    p, v = pos.clone(), vel.clone()
+    fused = pkg.integrators.FusedBarnesHut(pkg.Engine(0, n), p, v, name, 0.5, EPS)
+    for _ in range(steps):
+        fused.step(dt)
+    torch.cuda.synchronize()
+    assert torch.equal(p, want_p) and torch.equal(v, want_v)
+    # arguments that change on every call (a varying dt) are never captured and stay correct
+    q, w = pos.clone(), vel.clone()
+    sysm = pkg.integrators.ShardedSystem(eng, pos.clone(), vel.clone(), "bh", 2, EPS, 0.5)
+    integ = getattr(pkg.IntegrationMethods, name)()
+    integ.setSystem(sysm)
+    varying = pkg.integrators.FusedBarnesHut(pkg.Engine(0, n), q, w, name, 0.5, EPS)
+    for k in range(3):
+        integ.integrate(dt * (1 + k))
+        varying.step(dt * (1 + k))
+    torch.cuda.synchronize()
+    assert torch.equal(q, sysm.pos) and torch.equal(w, sysm.vel)
+    eng.close()
+
+
 @pytest.mark.parametrize("planar", [False, True])
 @pytest.mark.parametrize("name,world,n", [("Verlet_DKD", 3, 20000), ("PEFRL", 2, 8192), ("ForestRuth", 4, 5000),
-                                          ("Euler_Symplectic_DK", 8, 12345), ("Euler_Symplectic_KD", 2, 33)])
+                                          ("Euler_Symplectic_DK", 8, 12345), ("Euler_Symplectic_KD", 2, 33),
+                                          ("Verlet_DKD", 2, 270000)])
 def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n, planar):
     """`world` ranks emulated on one GPU (one engine and one replica of pos / vel each; the all-gather is a
     concatenation of the ranks' rows): after every step each replica equals the single-GPU trajectory bit for bit,
@@ -58,10 +88,10 @@ def test_sharded_rows_equal_separate_kernels(engine, pkg, name, world, n, planar
     pins it with NB_BH_WALK_SPLIT=1 for its two-rank comparison.)"""
     import torch
     I = pkg.integrators
-    dt, steps = 1.0e-3, 2
+    dt, steps = 1.0e-3, (2 if n <= 262144 else 4)      # above: first sighting, capture, two replays
     pos, vel = _state(pkg, n, 11, vz=not planar)
     flags = pkg.NB_BH_PLANAR if planar else 0
-    want_p, want_v = _classic(pkg, engine, name, pos, vel, dt, steps)
+    want_p, want_v = _classic(pkg, engine if n <= 262144 else pkg.Engine(0, n), name, pos, vel, dt, steps)
     groups = (n + 31) // 32
     ranks = []
     for r in range(world):
