@@ -99,6 +99,8 @@ struct nb_bh_state {
     };
     GraphKey graph_key{};
     cudaGraphExec_t graph_exec = nullptr;
+    GraphKey seen_key{};       // above 262,144 bodies: the last uncaptured call, captured if it comes again
+    bool seen_valid = false;
     cudaStream_t capture_stream = nullptr;
     // the fused step (nb_bh_step_groups) at launch-bound sizes: a few captured graphs, matched on every argument of the
     // call (a sharded stepper alternates between two rows arrays, a Forest-Ruth step between three coefficient sets)
@@ -1384,21 +1386,28 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     if (group_begin < 0 || group_count < 0 || group_begin + group_count > groups)
         return nb_fail(ctx, NB_ERR_INVALID, "group range outside [0, ceil(n/32))");
     NB_DEVICE(ctx);
-    static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 262144; }();
+    static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 2097152; }();
     const bool counting = (flags & NB_BH_COUNT_FLAG) != 0;
     rc = ensure_state(ctx, n);   // allocation must not happen inside a capture
     if (rc) return rc;
     pick_sort_mode(ctx->bh);
-    if (n > graph_max_n || n < 2 || counting) {
-        rc = run_build(ctx, pos, n, flags, 4, theta, (cudaStream_t)stream);
-        if (rc) return rc;
-        return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, counting, (cudaStream_t)stream);
-    }
-    // launch-bound sizes: replay a captured graph of the same evaluation
     nb_bh_state* st = ctx->bh;
     const int accumulate = ((flags & NB_BH_ACCUMULATE_BOUNDS) && st->bounds_valid) ? 1 : 0;
     const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening, st->sort_full,
                                       walk_qcap(), walk_forced_split()};
+    bool direct = n > graph_max_n || n < 2 || counting;
+    if (!direct && n > 262144 && !(st->graph_exec && st->graph_key == key)) {
+        // past the launch-bound sizes a capture costs more than it saves unless the call repeats: wait for the second one
+        direct = !(st->seen_valid && st->seen_key == key);
+        st->seen_key = key;
+        st->seen_valid = true;
+    }
+    if (direct) {
+        rc = run_build(ctx, pos, n, flags, 4, theta, (cudaStream_t)stream);
+        if (rc) return rc;
+        return run_walk(ctx, pos, acc, n, theta, softening, group_begin, group_count, counting, (cudaStream_t)stream);
+    }
+    // replay a captured graph of the same evaluation
     if (!st->graph_exec || !(st->graph_key == key)) {
         if (st->graph_exec) { cudaGraphExecDestroy(st->graph_exec); st->graph_exec = nullptr; }
         if (!st->capture_stream) NB_CUDA(ctx, cudaStreamCreateWithFlags(&st->capture_stream, cudaStreamNonBlocking));
