@@ -123,7 +123,7 @@ def run_reference_arm(args):
             "e2e": {"value": val, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "reference is GPU-only; this arm is the OpenMP transcription of its direct loop (oracle/)"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def ref_bh_worker(out_path):
@@ -157,9 +157,22 @@ def ref_bh_worker(out_path):
     print(json.dumps({"ms": tms}), flush=True)
 
 
+_RESULT_FD = 1
+
+
+def emit(line):
+    """The ONE JSON line of the run, on the process's original stdout."""
+    sys.stdout.flush()
+    os.write(_RESULT_FD, (json.dumps(line) + "\n").encode())
+
+
 def main():
     if len(sys.argv) == 3 and sys.argv[1] == "--ref-bh-worker":
         return ref_bh_worker(sys.argv[2])
+    # libraries write to fd 1 too (NCCL's version banner): everything but the result line goes to stderr
+    global _RESULT_FD
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -556,7 +569,7 @@ def main():
                 "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * (launches_force + 2),
                 "roofline": roofline, "cpu_baseline": cpu_baseline}
         line.update(extra)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     eng.close()

@@ -1396,6 +1396,9 @@ int nb_bh_accel_groups(nb_context* ctx, const float* pos, float* acc, int n, flo
     const nb_bh_state::GraphKey key{pos, acc, n, flags, group_begin, group_count, accumulate, theta, softening, st->sort_full,
                                       walk_qcap(), walk_forced_split()};
     bool direct = n > graph_max_n || n < 2 || counting;
+    // a slice of the groups means a sharded run, where a collective sits between two evaluations: measured at N = 1M on
+    // two GPUs, graph -> NCCL kernel -> graph transitions cost more (+35 us per step) than the launch gaps they remove
+    if (n > 262144 && group_count != groups) direct = true;
     if (!direct && n > 262144 && !(st->graph_exec && st->graph_key == key)) {
         // past the launch-bound sizes a capture costs more than it saves unless the call repeats: wait for the second one
         direct = !(st->seen_valid && st->seen_key == key);
@@ -1489,7 +1492,10 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     static const int graph_max_n = [] { const char* v = getenv("NB_BH_GRAPH_MAX_N"); return v ? atoi(v) : 2097152; }();
     constexpr int STEP_GRAPH_EAGER_N = 262144;
     const bool nothing_to_do = step->group_count == 0 && step->kick_kind == NB_KICK_NONE && step->drift_kind == NB_DRIFT_NONE;
-    if (n <= graph_max_n && n >= 2 && !nothing_to_do) {
+    // the sharded form (rows in or out) has a collective or a barrier between two calls: above the launch-bound sizes the
+    // graph -> NCCL kernel -> graph transitions cost more than the gaps a graph removes (N = 1M, 2 GPUs: 0.802 -> 0.838 ms)
+    const bool sharded_form = step->rows_in || step->rows_out || step->n_rows_peers > 0;
+    if (n <= graph_max_n && n >= 2 && !nothing_to_do && !(sharded_form && n > STEP_GRAPH_EAGER_N)) {
         // replay a captured graph of the same call
         struct Key {
             const float* pos; const float* vel; int n, accumulate, sort_full, qcap, split; const void* perm; nb_bh_step st;
