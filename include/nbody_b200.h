@@ -159,7 +159,8 @@ int nb_bh_export_tree(nb_context* ctx, int* n_cells, uint64_t* prefix, int32_t* 
 
 /* Counters of the last walk: nodes opened, children examined, lane interactions, max queue depth, nodes
  * in the tree, status flags (bit 0 = at least one group's node queue filled up and that group finished its walk in
- * depth-first order -- slower, same result; the counters [0..3] need NB_BH_COUNT_WALK, the status bit does not). */
+ * depth-first order -- slower, same result; bit 1 = a wait for the peers' rows (nb_bh_step::sync_local) timed out; the
+ * counters [0..3] need NB_BH_COUNT_WALK, the status bits do not). */
 int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]);
 
 /* Per-group work of the last NB_BH_COUNT_WALK evaluation: work[g] = records summed for each target of group g (bodies and
@@ -284,7 +285,18 @@ typedef struct nb_bh_step {
      * force evaluations by one cross-rank barrier (integrators.FusedBarnesHut(p2p=True)). */
     int n_rows_peers;
     float* rows_peers[NB_MAX_PEERS];
+    /* ... and without a barrier either: sync_local != NULL names this rank's sync array (unsigned int[NB_SYNC_WORDS] from
+     * nb_peer_alloc, zeroed once by the caller before any rank's first call), sync_peers[r] rank r's array mapped here
+     * (this rank's own among them) and sync_rank this rank's index.  After its walk the call counts the evaluation in
+     * word 8 of its own array and stores the count into word sync_rank of every rank's array; a call with rows_in waits,
+     * on the device and before it reads the rows, until words [0, n_rows_peers) of its own array have reached its own
+     * count.  No host synchronisation and no collective between consecutive force evaluations; every rank must make
+     * the same sequence of calls.  A wait that lasts 10 s gives up (nb_bh_last_counters status bit 1). */
+    int sync_rank;
+    unsigned int* sync_local;
+    unsigned int* sync_peers[NB_MAX_PEERS];
 } nb_bh_step;
+#define NB_SYNC_WORDS 16
 int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_bh_step* step, void* stream);
 
 /* The same for the direct sum, on a target slice: optional drift of the slice's bodies (done by the kernel that classifies

@@ -56,7 +56,8 @@ class BHStep(C.Structure):
                 ("drift_kind", C.c_int), ("drift_coef", C.c_double),
                 ("rows_in", C.c_void_p), ("prev_drift_kind", C.c_int), ("prev_drift_coef", C.c_double),
                 ("rows_out", C.c_void_p), ("acc_out", C.c_void_p), ("stats_out", C.c_void_p),
-                ("n_rows_peers", C.c_int), ("rows_peers", C.c_void_p * 8)]
+                ("n_rows_peers", C.c_int), ("rows_peers", C.c_void_p * 8),
+                ("sync_rank", C.c_int), ("sync_local", C.c_void_p), ("sync_peers", C.c_void_p * 8)]
 
 
 class PeerBuffer:
@@ -270,9 +271,10 @@ class Engine:
 
     def bh_step_groups(self, pos, vel, theta, softening, dt, group_begin, group_count, pre_drift=(0, 0.0), kick=(0, 0.0),
                        drift=(0, 0.0), rows_in=None, prev_drift=(0, 0.0), rows_out=None, acc_out=None, stats_out=None,
-                       flags=NB_BH_FRESH_BOUNDS, stream=None, rows_peers=None):
+                       flags=NB_BH_FRESH_BOUNDS, stream=None, rows_peers=None, sync=None):
         """One [pre-drift; force; kick; drift] group of a stepper with the kick and drift fused into the walk
-        (nb_bh_step_groups).  pos, vel: CUDA float32 [n,4], updated in place unless rows_out is given."""
+        (nb_bh_step_groups).  pos, vel: CUDA float32 [n,4], updated in place unless rows_out is given.
+        sync = (rank, [device pointer of every rank's sync array]): arrival words instead of a barrier between calls."""
         n = pos.shape[0]
         _check_tensor(pos, n), _check_tensor(vel, n)
         st = BHStep(theta, softening, dt, flags, group_begin, group_count, pre_drift[0], pre_drift[1], kick[0], kick[1],
@@ -284,6 +286,11 @@ class Engine:
             st.n_rows_peers = len(rows_peers)
             for k, ptr in enumerate(rows_peers):
                 st.rows_peers[k] = ptr
+        if sync is not None:
+            st.sync_rank = sync[0]
+            st.sync_local = sync[1][sync[0]]
+            for k, ptr in enumerate(sync[1]):
+                st.sync_peers[k] = ptr
         self._check(lib().nb_bh_step_groups(self._h, pos.data_ptr(), vel.data_ptr(), n, C.byref(st), _stream_ptr(stream)),
                     "nb_bh_step_groups")
 

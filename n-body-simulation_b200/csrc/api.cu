@@ -74,6 +74,9 @@ int nb_peer_alloc(nb_context* ctx, uint64_t bytes, void** ptr, unsigned char han
     if (!ctx || !ptr || !handle || bytes == 0) return ctx ? nb_fail(ctx, NB_ERR_INVALID, "nb_peer_alloc: bad argument") : NB_ERR_INVALID;
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     NB_DEVICE(ctx);
+    // small cudaMalloc blocks share a 2 MiB page with other allocations and an IPC handle exports whole pages: give
+    // every shared buffer pages of its own
+    if (bytes < (2ull << 20)) bytes = 2ull << 20;
     NB_CUDA(ctx, cudaMalloc(ptr, bytes));
     cudaIpcMemHandle_t h;
     cudaError_t e = cudaIpcGetMemHandle(&h, *ptr);

@@ -107,7 +107,7 @@ struct nb_bh_state {
     // Up to STEP_GRAPH_EAGER_N bodies a new argument set is captured at once; above, only when it comes a second time
     // (seen && !exec marks the first sighting), so a caller whose arguments change every call never pays for a capture.
     struct StepGraph {
-        unsigned char key[320];
+        unsigned char key[448];
         cudaGraphExec_t exec = nullptr;
         bool seen = false;
     };
@@ -139,7 +139,48 @@ struct PrepArgs {
     SubstepArgs pre;    // modes 1, 2: drift before this evaluation (NB_DRIFT_NONE: none)
     int planar;         // mode 2: the caller vouches for v_z = 0 everywhere, so z never moves: x, y, vx, vy are stored as two
                         // 8-byte halves and nothing is read back (half the scattered traffic)
+    // mode 2, rows stored by peers (nb_bh_step::sync_local): this rank's arrival words; the rows are complete once words
+    // [0, sync_n) have all reached word NB_SYNC_COUNT (this rank's own number of finished evaluations)
+    const unsigned int* sync_wait;
+    int sync_n;
 };
+
+constexpr int NB_SYNC_COUNT = 8;            // word of the sync array that counts this rank's finished evaluations
+constexpr unsigned long long SYNC_TIMEOUT_NS = 10ull * 1000ull * 1000ull * 1000ull;
+
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// After a rank's walk (same stream, so its row stores to the peers have completed): count the evaluation and tell every
+// rank, this one included, by storing the count into word `rank` of its sync array.  Plain stores to peer memory.
+struct SyncPeers {
+    unsigned int* local;
+    unsigned int* peer[NB_MAX_PEERS];
+    int n, rank;
+};
+__global__ void peer_signal_kernel(const SyncPeers sp) {
+    __shared__ unsigned int count_s;
+    if (threadIdx.x == 0) {
+        count_s = sp.local[NB_SYNC_COUNT] + 1u;
+        sp.local[NB_SYNC_COUNT] = count_s;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < sp.n) {
+        __threadfence_system();
+        st_release_sys(sp.peer[threadIdx.x] + sp.rank, count_s);
+    }
+}
 
 // What the walk does with a target's acceleration (nb_bh_step_groups): the kick and drift that follow the force
 // evaluation in the reference's steppers (src/IntegrationMethods.cu:81-93 and the other K+D kernels) run in the walk's
@@ -170,6 +211,24 @@ __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* par
                               unsigned int* __restrict__ ticket, float4* __restrict__ bounds, int accumulate,
                               unsigned long long* __restrict__ walk_status, const PrepArgs prep) {
     float mnx = FLT_MAX, mny = FLT_MAX, mxx = -FLT_MAX, mxy = -FLT_MAX;
+    if (prep.mode == 2 && prep.sync_wait) {
+        // the rows come from the peers' walks: wait until every rank has reported the evaluation this rank finished last
+        // (each block polls for itself -- no block depends on another one being resident).  Bounded: a peer that died
+        // leaves a count in walk_status[2] (nb_bh_last_counters status bit 1) instead of a hung GPU.
+        if (threadIdx.x == 0) {
+            const unsigned int want = prep.sync_wait[NB_SYNC_COUNT];
+            const unsigned long long t0 = global_timer_ns();
+            for (int r = 0; r < prep.sync_n; r++) {
+                while ((int)(ld_acquire_sys(prep.sync_wait + r) - want) < 0) {
+                    if (global_timer_ns() - t0 > SYNC_TIMEOUT_NS) {
+                        atomicAdd(walk_status + 2, 1ull);
+                        break;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         float4 p;
         if (prep.mode == 0) {
@@ -183,7 +242,7 @@ __global__ void bounds_kernel(const float4* __restrict__ pos, int n, float4* par
             prep.pos_rw[i] = p;
         } else {
             const int body = prep.perm[i];
-            const float4 r = prep.rows[i];
+            const float4 r = __ldcg(prep.rows + i);   // possibly written by a peer GPU: read at L2, this GPU's point of coherence
             if (prep.planar) {
                 p.x = drift1g(prep.pre, r.x, r.z, 0.f);
                 p.y = drift1g(prep.pre, r.y, r.w, 0.f);
@@ -1486,6 +1545,24 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     epi.row_base = step->group_begin * 32;
     epi.s = SubstepArgs{step->kick_kind, step->drift_kind, step->dt, step->kick_coef, step->drift_coef};
     epi.stats = step->stats_out;
+    // cross-rank ordering by arrival words instead of a barrier collective between two calls
+    SyncPeers sync{};
+    if (step->sync_local) {
+        if (step->n_rows_peers <= 0) return nb_fail(ctx, NB_ERR_INVALID, "sync_local needs rows_peers");
+        if (step->sync_rank < 0 || step->sync_rank >= step->n_rows_peers)
+            return nb_fail(ctx, NB_ERR_INVALID, "sync_rank outside [0, n_rows_peers)");
+        sync.local = step->sync_local;
+        sync.n = step->n_rows_peers;
+        sync.rank = step->sync_rank;
+        for (int r = 0; r < step->n_rows_peers; r++) {
+            if (!step->sync_peers[r]) return nb_fail(ctx, NB_ERR_INVALID, "sync_peers holds a NULL pointer");
+            sync.peer[r] = step->sync_peers[r];
+        }
+        if (prep.mode == 2) {
+            prep.sync_wait = step->sync_local;
+            prep.sync_n = step->n_rows_peers;
+        }
+    }
     pick_sort_mode(st);
     st->perm_valid = false;
     // replay pays up to a few million bodies (N = 1M: 1.126 -> 1.104 ms per step; the ~25 launches' gaps)
@@ -1494,7 +1571,7 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     const bool nothing_to_do = step->group_count == 0 && step->kick_kind == NB_KICK_NONE && step->drift_kind == NB_DRIFT_NONE;
     // the sharded form (rows in or out) has a collective or a barrier between two calls: above the launch-bound sizes the
     // graph -> NCCL kernel -> graph transitions cost more than the gaps a graph removes (N = 1M, 2 GPUs: 0.802 -> 0.838 ms)
-    const bool sharded_form = step->rows_in || step->rows_out || step->n_rows_peers > 0;
+    const bool sharded_form = (step->rows_in || step->rows_out || step->n_rows_peers > 0) && !sync.local;
     if (n <= graph_max_n && n >= 2 && !nothing_to_do && !(sharded_form && n > STEP_GRAPH_EAGER_N)) {
         // replay a captured graph of the same call
         struct Key {
@@ -1525,6 +1602,7 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
             if (!rc && step->group_count > 0)
                 rc = run_walk(ctx, pos, step->acc_out, n, step->theta, eps, step->group_begin, step->group_count, false,
                               st->capture_stream, epi);
+            if (!rc && sync.local) peer_signal_kernel<<<1, 32, 0, st->capture_stream>>>(sync);
             cudaGraph_t graph = nullptr;
             cudaError_t e = cudaStreamEndCapture(st->capture_stream, &graph);
             if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -1549,6 +1627,7 @@ int nb_bh_step_groups(nb_context* ctx, float* pos, float* vel, int n, const nb_b
     if (only_prep) return NB_OK;
     rc = run_walk(ctx, pos, step->acc_out, n, step->theta, eps, step->group_begin, step->group_count, false, stream, epi);
     if (rc) return rc;
+    if (sync.local) peer_signal_kernel<<<1, 32, 0, stream>>>(sync);   // also for a rank that owns no groups
     st->perm_valid = true;
     return NB_OK;
 }
@@ -1712,7 +1791,7 @@ int nb_bh_last_counters(nb_context* ctx, int64_t counters[6]) {
         nodes = a + b;
     }
     counters[0] = (int64_t)c[0]; counters[1] = (int64_t)c[1]; counters[2] = (int64_t)c[2]; counters[3] = (int64_t)c[3];
-    counters[4] = nodes; counters[5] = (int64_t)c[4];
+    counters[4] = nodes; counters[5] = (int64_t)(c[4] | (c[6] ? 2ull : 0ull));
     return NB_OK;
 }
 

@@ -6,6 +6,7 @@ nb_integrate_substep calls on the rank's target slice, 
 
 `system` must provide: engine, pos (replicated [N,4]), vel / acc (slice-local), begin, count, force(), gather().
 """
+import os
 import numpy as np
 
 KICK_NONE, KICK_F32, KICK_HALF_F64, KICK_COEF_F64, KICK_DTA_F64, KICK_MEAN_F64 = range(6)
@@ -214,19 +215,21 @@ class FusedBarnesHut:
         if self.p2p:
             # every rank maps every other rank's two rows arrays; if any rank cannot (no peer access between the GPUs, no
             # IPC between the processes), all ranks fall back to the all-gather together
-            shape = (32 * self.groups, 4)
+            # two rows arrays (alternating) and the 16 arrival words of nb_bh_step::sync_local
+            shapes = [(32 * self.groups, 4), (32 * self.groups, 4), (16,)]
             ok, opened = 1, []
             try:
-                self._mine = [engine.peer_alloc(shape) for _ in range(2)]
+                self._mine = [engine.peer_alloc(sh) for sh in shapes]
+                self._mine[2].tensor.zero_()
                 mine = [b.handle for b in self._mine]
             except Exception:
-                ok, mine, self._mine = 0, [None, None], []
+                ok, mine, self._mine = 0, [None, None, None], []
             handles = [None] * world
             dist.all_gather_object(handles, mine)
             if ok and all(h[0] is not None for h in handles):
                 try:
-                    self._peers = [[self._mine[k] if r == rank else engine.peer_open(handles[r][k], shape)
-                                    for r in range(world)] for k in range(2)]
+                    self._peers = [[self._mine[k] if r == rank else engine.peer_open(handles[r][k], shapes[k])
+                                    for r in range(world)] for k in range(3)]
                     opened = [b for row in self._peers for b in row if b.opened]
                 except Exception:
                     ok = 0
@@ -235,9 +238,11 @@ class FusedBarnesHut:
             flag = torch.tensor([float(ok)], device=pos.device)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)      # also: everyone has mapped everyone before the first store
             if flag.item() >= 1.0:
-                self._rows = [b.tensor for b in self._mine]
+                self._rows = [b.tensor for b in self._mine[:2]]
                 self._flip = 0
                 self._token = torch.zeros(1, device=pos.device)
+                # NB_BH_SYNC=0: one tiny all-reduce as the barrier between evaluations instead of the arrival words
+                self._sync = (rank, [b.ptr for b in self._peers[2]]) if os.environ.get("NB_BH_SYNC", "1") != "0" else None
             else:
                 for b in opened + list(self._mine):
                     b.release()
@@ -246,15 +251,20 @@ class FusedBarnesHut:
     def close(self):
         """Unmaps the other ranks' rows arrays and frees this rank's (p2p); call on every rank before the engine goes."""
         if self.p2p:
+            import torch
+            torch.cuda.synchronize()
+            self.dist.barrier()          # no rank may still be storing into an array that is about to go
             for row in self._peers:
                 for b in row:
                     b.release()
             self.p2p = False
 
     def _exchange(self):
-        """What follows a rank's walk: the all-gather of the rows, or (p2p) the barrier behind the peer stores."""
+        """What follows a rank's walk: the all-gather of the rows, or (p2p) the barrier behind the peer stores -- unless
+        the calls order themselves through the arrival words (nb_bh_step::sync_local), then nothing."""
         if self.p2p:
-            self.dist.all_reduce(self._token)
+            if self._sync is None:
+                self.dist.all_reduce(self._token)
         else:
             self._gather_rows()
 
@@ -275,7 +285,7 @@ class FusedBarnesHut:
             rows_in = self._rows[self._flip ^ 1] if self.pending is not None else None
             e.bh_step_groups(self.pos, self.vel, self.theta, self.eps, dt, self.g0, self.g1 - self.g0, pre_drift=pre, kick=kick,
                              drift=drift, rows_in=rows_in, prev_drift=prev, rows_peers=[b.ptr for b in self._peers[self._flip]],
-                             stats_out=self.stats_buf if stats else None, flags=self.flags)
+                             stats_out=self.stats_buf if stats else None, flags=self.flags, sync=self._sync)
             self.force_evaluations += 1
             self._exchange()                      # barrier: every rank's stores of this evaluation have landed
             self.rows_all = self._rows[self._flip]
@@ -293,8 +303,11 @@ class FusedBarnesHut:
     def materialize(self):
         """Brings pos / vel (body order) up to date on this rank; a no-op on one GPU."""
         if self.pending is not None:
+            extra = {}
+            if self.p2p and self._sync is not None:     # the scatter waits for every rank's rows on the device
+                extra = dict(rows_peers=[b.ptr for b in self._peers[self._flip]], sync=self._sync)
             self.engine.bh_step_groups(self.pos, self.vel, self.theta, self.eps, self.pending[1], 0, 0, rows_in=self.rows_all,
-                                       prev_drift=self.pending[0], flags=self.flags)
+                                       prev_drift=self.pending[0], flags=self.flags, **extra)
             self.pending = None
 
     def step(self, dt, lazy=False, stats=False):

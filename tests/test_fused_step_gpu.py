@@ -237,6 +237,60 @@ def test_rows_stored_through_peer_pointers_equal_rows_out(engine, pkg):
         engine.bh_step_groups(pos, vel, 0.5, EPS, dt, 0, 1, rows_peers=[0])
 
 
+@pytest.mark.parametrize("name,world,n,steps", [("Verlet_DKD", 2, 20000, 3), ("PEFRL", 3, 8192, 2), ("ForestRuth", 8, 12345, 2),
+                                                ("Verlet_DKD", 2, 270000, 4)])
+def test_arrival_words_order_the_ranks_without_a_barrier(pkg, name, world, n, steps):
+    """nb_bh_step::sync_local: `world` ranks emulated on one GPU, every rank storing its rows into every rank's arrays and
+    counting its evaluations into every rank's arrival words; the calls are merely issued in turn on one stream -- no host
+    synchronisation, no collective, no copy between them -- and the next call's first kernel waits on the words.  Every
+    replica must follow the single-GPU trajectory bit for bit; the word arrays must end at the number of evaluations.
+    (n = 270,000: above the size where an argument set is captured into a graph on its second sighting.)"""
+    import torch
+    I = pkg.integrators
+    dt = 1.0e-3
+    pos, vel = _state(pkg, n, 13, vz=False)
+    ref_eng = pkg.Engine(0, n)
+    want_p, want_v = _classic(pkg, ref_eng, name, pos, vel, dt, steps)
+    groups = (n + 31) // 32
+    ranks = []
+    for r in range(world):
+        g0, g1 = pkg.shard.group_bounds(n, world, r)
+        ranks.append(dict(eng=pkg.Engine(0, n), pos=pos.clone(), vel=vel.clone(), g0=g0, g1=g1,
+                          rows=[torch.full((32 * groups, 4), float("nan"), device="cuda") for _ in range(2)],
+                          words=torch.zeros(16, dtype=torch.int32, device="cuda")))
+    sync_ptrs = [rk["words"].data_ptr() for rk in ranks]
+    flip, pending, evaluations = 0, None, 0
+    for _ in range(steps):
+        pre, prog = I.stepper_program(name, dt)
+        for k, (kick, drift) in enumerate(prog):
+            for r, rk in enumerate(ranks):
+                rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, rk["g0"], rk["g1"] - rk["g0"],
+                                         pre_drift=pre if k == 0 else (0, 0.0), kick=kick, drift=drift,
+                                         rows_in=rk["rows"][flip ^ 1] if pending is not None else None,
+                                         prev_drift=pending if pending is not None else (0, 0.0),
+                                         rows_peers=[q["rows"][flip].data_ptr() for q in ranks], sync=(r, sync_ptrs),
+                                         flags=pkg.NB_BH_PLANAR)
+            flip ^= 1
+            pending = drift
+            evaluations += 1
+    for r, rk in enumerate(ranks):                            # materialize: waits on the words too
+        rk["eng"].bh_step_groups(rk["pos"], rk["vel"], 0.5, EPS, dt, 0, 0, rows_in=rk["rows"][flip ^ 1], prev_drift=pending,
+                                 rows_peers=[q["rows"][flip].data_ptr() for q in ranks], sync=(r, sync_ptrs),
+                                 flags=pkg.NB_BH_PLANAR)
+    torch.cuda.synchronize()
+    for rk in ranks:
+        assert torch.equal(rk["pos"], want_p) and torch.equal(rk["vel"], want_v)
+        w = rk["words"].tolist()
+        assert w[:world] == [evaluations] * world and w[8] == evaluations
+        assert rk["eng"].bh_last_counters()["status"] & 2 == 0      # no wait timed out
+        rk["eng"].close()
+    ref_eng.close()
+    with pytest.raises(pkg.NbodyError):                      # the words need the pointer list they index
+        e = pkg.Engine(0, 64)
+        p, v = _state(pkg, 64, 3)
+        e.bh_step_groups(p, v, 0.5, EPS, dt, 0, 2, sync=(0, [sync_ptrs[0]]))
+
+
 def test_replayed_graph_and_pending_rows_survive_other_calls(pkg):
     """Two hazards of cached state.  (i) The fused direct step replays a captured graph at small sizes; a larger call in
     between moves the scratch the graph points to, so the graph must be rebuilt, not replayed.  (ii) rows_in refers to the
