@@ -401,6 +401,7 @@ def main():
             p2p = world > 1 and os.environ.get("NB_BH_P2P", "1") != "0"
             stepper = pkg.integrators.FusedBarnesHut(eng, p2, v2, "Verlet_DKD", THETA, EPS, world, rank, dist, p2p=p2p)
             p2p = stepper.p2p      # False if the ranks could not map each other's memory (they then fall back together)
+            words = p2p and getattr(stepper, "_sync", None) is not None
             coll_events = []
             if world > 1:
                 plain_gather = stepper._exchange
@@ -439,8 +440,11 @@ def main():
                   "ms_per_step": bh_ms, "n": nb, "theta": THETA,
                   "step": "Verlet_DKD: drift (fused into the bounds kernel) + build + walk with kick/drift epilogue"
                           + ((" + rows (16 B/body) stored into every rank's array by the walk epilogue over NVLink peer memory, "
-                              "one 4-byte all-reduce as barrier" if p2p else " + all-gather of 16 B/body rows (NCCL)") if world > 1 else ""),
-                  "exchange": ("peer stores in the walk epilogue + barrier" if p2p else "NCCL all-gather") if world > 1 else None,
+                              + ("evaluations ordered by arrival words the ranks store into each other's memory (no collective)"
+                                 if words else "one 4-byte all-reduce as barrier")
+                              if p2p else " + all-gather of 16 B/body rows (NCCL)") if world > 1 else ""),
+                  "exchange": ("peer stores in the walk epilogue + " + ("arrival words" if words else "barrier")
+                               if p2p else "NCCL all-gather") if world > 1 else None,
                   "collective_ms_per_step": coll_ms, "collective_bytes_per_step": nb * 16 if world > 1 else 0,
                   "force_evaluation_ms": eval_ms, "force_evaluation_ms_per_rank_warm_l2": per_rank,
                   "force_evaluation_note": "nb_bh_accel_groups alone on this rank's groups (build + walk, no kick/drift, no collective)"}

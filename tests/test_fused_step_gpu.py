@@ -244,7 +244,7 @@ def test_arrival_words_order_the_ranks_without_a_barrier(pkg, name, world, n, st
     counting its evaluations into every rank's arrival words; the calls are merely issued in turn on one stream -- no host
     synchronisation, no collective, no copy between them -- and the next call's first kernel waits on the words.  Every
     replica must follow the single-GPU trajectory bit for bit; the word arrays must end at the number of evaluations.
-    (n = 270,000: above the size where an argument set is captured into a graph on its second sighting.)"""
+    (n = 270,000: above the sizes at which the sharded form is replayed from a graph.)"""
     import torch
     I = pkg.integrators
     dt = 1.0e-3
